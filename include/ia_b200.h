@@ -1,0 +1,166 @@
+/*
+ * ia_b200.h — C ABI of libia_b200.so: the B200 (sm_100a) implementation of
+ * Inference Arena's `shared.processing` hot path.
+ *
+ * Conventions
+ *   - Plain pointers and sizes only.  Pointers named *_dev are device pointers on the
+ *     CURRENT CUDA device; `stream` is a cudaStream_t passed as void* (NULL = default
+ *     stream).  Calls are stream-ordered, never synchronise and never allocate unless
+ *     the comment says otherwise.  Safe to call concurrently on different streams as
+ *     long as the buffers (including `workspace`) are distinct.
+ *   - Return value: 0 = success; > 0 = a cudaError_t from the launch; < 0 = IA_ERR_*.
+ *   - All float arithmetic that the reference does in numpy float32 is done in IEEE
+ *     float32 with round-to-nearest and no FMA contraction; OpenCV's 8-bit INTER_LINEAR
+ *     is reproduced in its own 11-bit fixed point, so results are bit-identical to the
+ *     reference's CPU path.
+ *   - Every declaration cites the reference interface it replaces
+ *     (paths relative to the reference repository root).
+ */
+#ifndef IA_B200_H
+#define IA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IA_OK 0
+#define IA_ERR_INVALID_ARGUMENT (-1)
+#define IA_ERR_WORKSPACE_TOO_SMALL (-2)
+#define IA_ERR_UNSUPPORTED (-3)
+#define IA_ERR_CAPACITY (-4)
+
+#define IA_HEAD_LAYOUT_V5 0 /* (N, A, 5+C): cx,cy,w,h,obj,cls...   curator.py:289-307 */
+#define IA_HEAD_LAYOUT_V8 1 /* (N, 4+C, A): channel-major, no obj   postprocess.py:33-41 */
+
+/* Library / build identification ("ia_b200 <version> sm_100a"). */
+const char* ia_version(void);
+/* Human-readable text for a return value of any function below. */
+const char* ia_error_string(int code);
+
+/* ---------------------------------------------------------------------------------
+ * Letterbox geometry — host scalars of letterbox(), src/shared/processing/
+ * transforms.py:150-157,174-175: scale = min(T/h, T/w) in float64, new = int(dim*scale)
+ * (truncation), pad = (T - new) // 2.  Pure host arithmetic, no CUDA.
+ * ------------------------------------------------------------------------------- */
+typedef struct ia_letterbox_geom {
+  int32_t src_h, src_w, target;
+  int32_t new_h, new_w;
+  int32_t pad_h, pad_w;
+  double scale;
+} ia_letterbox_geom;
+int ia_letterbox_geometry(int src_h, int src_w, int target, ia_letterbox_geom* out);
+
+/* ---------------------------------------------------------------------------------
+ * K1 — fused letterbox + /divisor + HWC->CHW for a batch of equally-sized frames.
+ * Replaces YOLOPreprocessor.preprocess, src/shared/processing/yolo_preprocess.py:128-174
+ * (letterbox transforms.py:118-180, astype(f32)/255.0 :158, transpose :161, contiguous
+ * :167) applied to each of the n frames.
+ *   frames_dev  uint8 [n, src_h, src_w, 3]
+ *   out_dev     float [n, 3, target, target]
+ * ------------------------------------------------------------------------------- */
+int ia_yolo_preprocess(const uint8_t* frames_dev, int n, int src_h, int src_w, int target,
+                       float divisor, float* out_dev, void* stream);
+
+/* letterbox() itself, transforms.py:118-180: uint8 [n, target, target, 3] HWC with the
+ * padding colour `pad_rgb` (LETTERBOX_COLOR, transforms.py:37). */
+int ia_letterbox_u8(const uint8_t* frames_dev, int n, int src_h, int src_w, int target,
+                    const uint8_t pad_rgb[3], uint8_t* out_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------
+ * K2 + K3 — YOLO head decode, confidence filter + stream compaction, per-class greedy
+ * NMS and row assembly, for a batch of n images, entirely on the device.
+ * Replaces, per image: DetectionCounter._parse_yolov5_raw_output, src/shared/data/
+ * curator.py:289-307 (conf = obj * max(cls), class = argmax) or the v8 parse,
+ * architectures/monolithic/app/postprocess.py:33-41; apply_nms, postprocess.py:76-160
+ * (== curator.py:323-400); and the output assembly postprocess.py:52-73.
+ *   head_dev         float, layout per `layout` (IA_HEAD_LAYOUT_*), n images
+ *   max_candidates   capacity of the per-image candidate list (anchors passing the
+ *                    confidence filter); `anchors` is always sufficient
+ *   max_det          rows available per image in dets_dev / keep_dev
+ *   dets_dev         float [n, max_det, 6]  rows [x1,y1,x2,y2,conf,class], class-ascending
+ *                    then confidence-descending — the order apply_nms returns
+ *   keep_dev         int32 [n, max_det]     original anchor index of each row
+ *   count_dev        int32 [n]              detections kept per image
+ *   status_dev       int32 [n]              0 ok; bit0 = candidate list overflowed
+ *                    (> max_candidates), bit1 = more than max_det kept.  Rows are exact
+ *                    whenever the status is 0.
+ *   workspace        device scratch of at least ia_decode_nms_workspace_bytes(...)
+ * Equal confidences inside one class (order undefined in the reference, postprocess.py:
+ * 129) are ordered larger-anchor-index first.
+ * ------------------------------------------------------------------------------- */
+size_t ia_decode_nms_workspace_bytes(int n, int anchors, int max_candidates);
+int ia_decode_nms(const float* head_dev, int layout, int n, int anchors, int num_classes,
+                  float conf_threshold, float iou_threshold, int max_candidates, int max_det,
+                  float* dets_dev, int32_t* keep_dev, int32_t* count_dev, int32_t* status_dev,
+                  void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* apply_nms() on already-decoded arrays, postprocess.py:76-160: boxes [m,4] cx,cy,w,h,
+ * scores [m], class ids int32 [m] -> keep_dev int32 [max_det] (original indices),
+ * count_dev [1], status_dev [1].  Workspace: ia_decode_nms_workspace_bytes(1, m, m). */
+int ia_nms(const float* boxes_dev, const float* scores_dev, const int32_t* class_ids_dev, int m,
+           float conf_threshold, float iou_threshold, int max_det, int32_t* keep_dev,
+           int32_t* count_dev, int32_t* status_dev, void* workspace_dev, size_t workspace_bytes,
+           void* stream);
+
+/* ---------------------------------------------------------------------------------
+ * scale_boxes(), src/shared/processing/transforms.py:183-230 (also
+ * YOLOPreprocessResult.scale_boxes_to_original, yolo_preprocess.py:60-69): un-pad,
+ * divide by float32(scale), clip to the original frame; columns >= 4 are copied.
+ *   boxes_dev float [m, cols] -> out_dev float [m, cols]   (cols >= 4)
+ * ------------------------------------------------------------------------------- */
+int ia_scale_boxes(const float* boxes_dev, int m, int cols, float scale, int pad_w, int pad_h,
+                   int orig_h, int orig_w, float* out_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------
+ * K4 — fan-out: for every kept detection, scale_boxes -> extract_crop -> bilinear resize
+ * to out_size x out_size -> ImageNet normalise -> CHW, reading the NMS output on the
+ * device.  Replaces the per-detection loop of architectures/monolithic/app/inference.py:
+ * 188-193: scale_boxes_to_original (yolo_preprocess.py:60-69), extract_crop
+ * (src/shared/processing/mobilenet_preprocess.py:236-269: truncating int(), clamp,
+ * empty -> 1x1 zeros), MobileNetPreprocessor.preprocess (mobilenet_preprocess.py:114-160)
+ * and imagenet_normalize (transforms.py:238-272).
+ *   frames_dev      uint8 [n, src_h, src_w, 3]  original-resolution frames
+ *   dets_dev        float [n, max_det, 6]       letterbox-space rows from ia_decode_nms
+ *   count_dev       int32 [n]
+ *   scale,pad_*     letterbox geometry of the frames (ia_letterbox_geometry)
+ *   mean,std        float[3] each (experiment.yaml:244-245)
+ *   crops_dev       float [roi_capacity, 3, out_size, out_size]; ROI r of image i, k-th
+ *                   detection, is r = roi_offsets[i] + k
+ *   roi_offsets_dev int32 [n+1] exclusive scan of min(count, max_det); [n] = total ROIs
+ *   rois_dev        int32 [roi_capacity, 8] scratch/out: {image, x1, y1, x2, y2, empty,0,0}
+ *                   (the integer crop rectangle extract_crop would use)
+ * ROIs beyond roi_capacity are not written (roi_offsets still reports the true total).
+ * ------------------------------------------------------------------------------- */
+int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int src_h, int src_w,
+                             const float* dets_dev, const int32_t* count_dev, int max_det,
+                             float scale, int pad_w, int pad_h, int out_size,
+                             const float mean[3], const float std[3], float* crops_dev,
+                             int roi_capacity, int32_t* roi_offsets_dev, int32_t* rois_dev,
+                             void* stream);
+
+/* The same resize+normalise+CHW on explicit rectangles (no detection input):
+ * rois_dev int32 [num_rois, 8] as above.  With one ROI covering a whole image this is
+ * MobileNetPreprocessor.preprocess (mobilenet_preprocess.py:114-160) on a uint8 crop. */
+int ia_resize_normalize_rois(const uint8_t* frames_dev, int n, int src_h, int src_w,
+                             const int32_t* rois_dev, int num_rois, int out_size,
+                             const float mean[3], const float std[3], float* crops_dev,
+                             void* stream);
+
+/* extract_crop()'s rectangle, src/shared/processing/mobilenet_preprocess.py:256-267, for m
+ * boxes already in original-frame coordinates: int() truncation toward zero, clamp to the
+ * frame, empty test.  boxes_dev float [m, cols>=4] -> rois_dev int32 [m, 8]
+ * {image_index, x1, y1, x2, y2, empty, 0, 0} (the record ia_resize_normalize_rois takes). */
+int ia_extract_crop_rects(const float* boxes_dev, int m, int cols, int image_index, int src_h,
+                          int src_w, int32_t* rois_dev, void* stream);
+
+/* imagenet_normalize() on uint8 HWC, transforms.py:238-272 -> float HWC (same layout). */
+int ia_imagenet_normalize_u8(const uint8_t* image_dev, size_t pixels, const float mean[3],
+                             const float std[3], float* out_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IA_B200_H */

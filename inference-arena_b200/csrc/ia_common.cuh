@@ -1,0 +1,150 @@
+// ia_common.cuh — shared device helpers for the sm_100a kernels of libia_b200.
+//
+//  * mbarrier + 1-D bulk async copy (TMA engine, `cp.async.bulk`, SASS UBLKCP) used to
+//    stage frame rows / head tiles into shared memory;
+//  * the OpenCV INTER_LINEAR coefficient tables reproduced in device code
+//    (resize.cpp, 8-bit path — see oracle/cv_resize.py for the restated algorithm);
+//  * IEEE float helpers that can never be contracted into FMAs (numpy parity).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ia_b200.h"
+
+namespace ia {
+
+// ----------------------------------------------------------------------------- errors
+#define IA_RETURN_IF(cond, code) \
+  do {                           \
+    if (cond) return (code);     \
+  } while (0)
+
+inline int launch_status() {
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? IA_OK : (int)e;
+}
+
+// ------------------------------------------------------------------- mbarrier / bulk copy
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t arrivals) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals));
+}
+
+// make the barrier initialisation visible to the async (TMA) proxy
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(done)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return done != 0;
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// global -> shared 1-D bulk copy; dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes,
+                                         uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// ------------------------------------------------------------------ streaming load/store
+__device__ __forceinline__ void st_stream_f4(float* p, float a, float b, float c, float d) {
+  asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void st_stream_f1(float* p, float a) {
+  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
+}
+
+// ------------------------------------------------------------ OpenCV linear coefficients
+constexpr int kCoefOne = 2048;  // INTER_RESIZE_COEF_SCALE (11 bits)
+
+enum ResizeMode : int { kResizeCopy = 0, kResizeBox2 = 1, kResizeLinear = 2 };
+
+__host__ __device__ __forceinline__ int resize_mode(int src_h, int src_w, int dst_h, int dst_w) {
+  if (src_h == dst_h && src_w == dst_w) return kResizeCopy;        // resize.cpp: dsize == ssize
+  if (src_h == 2 * dst_h && src_w == 2 * dst_w) return kResizeBox2;  // is_area_fast, iscale == 2
+  return kResizeLinear;
+}
+
+struct AxisCoef {
+  int s0;  // first source index (clamped on X; raw floor on Y)
+  int w0;  // coefficient of s0     (0..2048)
+  int w1;  // coefficient of s0 + 1 (0..2048)
+};
+
+// OpenCV's scale_x / scale_y: 1. / ((double)dst / src)  (cv::resize, resize.cpp).
+__host__ __device__ __forceinline__ double axis_scale(int dst, int src) {
+#ifdef __CUDA_ARCH__
+  return __ddiv_rn(1.0, __ddiv_rn((double)dst, (double)src));
+#else
+  volatile double inv = (double)dst / (double)src;
+  return 1.0 / inv;
+#endif
+}
+
+// One entry of the xofs/alpha (zero_frac_at_border = true) or yofs/beta table.
+// Every operation is an explicit round-to-nearest intrinsic: nvcc must not fuse
+// (i + 0.5) * sc - 0.5 into an FMA, OpenCV's x86 baseline build does not.
+__device__ __forceinline__ AxisCoef axis_coef(int i, double sc, int src, bool zero_frac_at_border) {
+  const double pos = __dsub_rn(__dmul_rn(__dadd_rn((double)i, 0.5), sc), 0.5);
+  float f = __double2float_rn(pos);
+  int s0 = __float2int_rd(f);
+  f = __fsub_rn(f, (float)s0);
+  if (zero_frac_at_border) {
+    if (s0 < 0) {
+      s0 = 0;
+      f = 0.f;
+    }
+    if (s0 >= src - 1) {
+      s0 = src - 1;
+      f = 0.f;
+    }
+  }
+  AxisCoef c;
+  c.s0 = s0;
+  c.w1 = __float2int_rn(__fmul_rn(f, (float)kCoefOne));
+  c.w0 = __float2int_rn(__fmul_rn(__fsub_rn(1.f, f), (float)kCoefOne));
+  return c;
+}
+
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// VResizeLinear<uchar,int,short>: ((b0*(h0>>4))>>16) + ((b1*(h1>>4))>>16) + 2) >> 2
+__device__ __forceinline__ int vresize(int h0, int h1, int b0, int b1) {
+  return (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+}
+
+// numpy.maximum / numpy.minimum propagate NaN; fmaxf/fminf do not.
+__device__ __forceinline__ float np_max(float a, float b) { return (a != a) ? a : ((b != b) ? b : fmaxf(a, b)); }
+__device__ __forceinline__ float np_min(float a, float b) { return (a != a) ? a : ((b != b) ? b : fminf(a, b)); }
+
+}  // namespace ia

@@ -1,0 +1,372 @@
+// ia_crop.cu — K4: batched ROI crop -> bilinear resize -> ImageNet normalise -> CHW, fed by
+// the NMS output on the device (no host round trip), plus the small box/normalise ops.
+//
+// Replaces the per-detection loop of the reference (architectures/monolithic/app/
+// inference.py:188-193): scale_boxes (src/shared/processing/transforms.py:183-230),
+// extract_crop (mobilenet_preprocess.py:236-269), MobileNetPreprocessor.preprocess
+// (mobilenet_preprocess.py:114-160) and imagenet_normalize (transforms.py:238-272).
+//
+// Stage A (one CTA): exclusive scan of the per-image detection counts -> roi_offsets, and
+// for every detection the float32 box arithmetic of scale_boxes followed by extract_crop's
+// truncation/clamp -> an integer rectangle per ROI.
+// Stage B (one CTA per ROI row-group): OpenCV's 8-bit INTER_LINEAR (copy / 2x2 box /
+// 11-bit fixed-point bilinear, bit-identical to cv2.resize), a 3x256 LUT holding
+// ((v/255) - mean) / std computed with the reference's float32 operations, and coalesced
+// 128-bit plane stores.  HBM traffic: crop pixels + 3*S*S floats per ROI.
+#include "ia_common.cuh"
+
+namespace ia {
+
+constexpr int kRoiThreads = 1024;
+constexpr int kCropThreads = 128;
+constexpr int kCropRows = 8;
+constexpr int kRoiInts = 8;
+
+// ------------------------------------------------------------------------------ stage A
+struct RoiParams {
+  const float* dets;
+  const int* count;
+  int n, max_det;
+  float scale;
+  int pad_w, pad_h, src_h, src_w;
+  int roi_capacity;
+  int* offsets;  // [n+1]
+  int* rois;     // [capacity, 8]
+};
+
+// transforms.py:216-228 for one coordinate: (v - pad) / float32(scale), clip to [0, hi].
+__device__ __forceinline__ float unletterbox(float v, int pad, float scale, int hi) {
+  const float t = __fdiv_rn(__fsub_rn(v, (float)pad), scale);
+  return np_min(np_max(t, 0.f), (float)hi);
+}
+
+__device__ __forceinline__ void write_roi(int* roi, int img, float fx1, float fy1, float fx2,
+                                          float fy2, int src_h, int src_w) {
+  // mobilenet_preprocess.py:256-267: int() truncates toward zero, then clamp.
+  int x1 = max(0, __float2int_rz(fx1));
+  int y1 = max(0, __float2int_rz(fy1));
+  int x2 = min(src_w, __float2int_rz(fx2));
+  int y2 = min(src_h, __float2int_rz(fy2));
+  const int empty = (x2 <= x1 || y2 <= y1) ? 1 : 0;
+  roi[0] = img;
+  roi[1] = x1;
+  roi[2] = y1;
+  roi[3] = x2;
+  roi[4] = y2;
+  roi[5] = empty;
+  roi[6] = 0;
+  roi[7] = 0;
+}
+
+__global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams p) {
+  __shared__ int warp_sums[32];
+  __shared__ int carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < p.n; base += kRoiThreads) {
+    const int i = base + tid;
+    const int c = i < p.n ? min(max(p.count[i], 0), p.max_det) : 0;
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_sums[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += t;
+      }
+      warp_sums[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const int before = carry + (warp ? warp_sums[warp - 1] : 0) + incl - c;
+    if (i < p.n) {
+      p.offsets[i] = before;
+      for (int k = 0; k < c; ++k) {
+        const int r = before + k;
+        if (r < p.roi_capacity) {
+          const float* d = p.dets + ((size_t)i * p.max_det + k) * 6;
+          write_roi(p.rois + (size_t)r * kRoiInts, i, unletterbox(d[0], p.pad_w, p.scale, p.src_w),
+                    unletterbox(d[1], p.pad_h, p.scale, p.src_h),
+                    unletterbox(d[2], p.pad_w, p.scale, p.src_w),
+                    unletterbox(d[3], p.pad_h, p.scale, p.src_h), p.src_h, p.src_w);
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0) carry += warp_sums[31];
+    __syncthreads();
+  }
+  if (tid == 0) p.offsets[p.n] = carry;
+}
+
+// ------------------------------------------------------------------------------ stage B
+struct CropParams {
+  const uint8_t* frames;
+  int src_h, src_w;
+  const int* rois;
+  const int* total_dev;  // number of valid ROIs (device) or null
+  int total_host;        // used when total_dev is null
+  int roi_slots;         // ROIs the grid covers
+  int out_size, groups;
+  float mean[3], stdv[3];
+  float* out;
+};
+
+__global__ void __launch_bounds__(kCropThreads) crop_resize_kernel(const CropParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ float lut[3][256];
+  __shared__ int yplan[kCropRows][4];  // r0, r1, b0, b1
+
+  const int tid = threadIdx.x;
+  const int r = blockIdx.x / p.groups;
+  const int y_begin = (blockIdx.x - r * p.groups) * kCropRows;
+  const int total = p.total_dev ? min(*p.total_dev, p.roi_slots) : p.total_host;
+  if (r >= total) return;
+  const int S = p.out_size;
+  const int rows = min(kCropRows, S - y_begin);
+  int2* xtab = reinterpret_cast<int2*>(smem);
+
+  const int* roi = p.rois + (size_t)r * kRoiInts;
+  const int img = roi[0];
+  const int empty = roi[5];
+  const int rx1 = roi[1], ry1 = roi[2];
+  const int cw = empty ? 1 : roi[3] - roi[1];
+  const int ch = empty ? 1 : roi[4] - roi[2];
+  const int mode = resize_mode(ch, cw, S, S);
+  const size_t row_bytes = (size_t)p.src_w * 3;
+  const uint8_t* crop = p.frames + (size_t)img * p.src_h * row_bytes + (size_t)ry1 * row_bytes + (size_t)rx1 * 3;
+
+  for (int v = tid; v < 256; v += kCropThreads) {
+    const float u = __fdiv_rn((float)v, 255.0f);  // transforms.py:263
+#pragma unroll
+    for (int c = 0; c < 3; ++c) lut[c][v] = __fdiv_rn(__fsub_rn(u, p.mean[c]), p.stdv[c]);  // :270
+  }
+  if (mode == kResizeLinear) {
+    const double sc_x = axis_scale(S, cw);
+    for (int dx = tid; dx < S; dx += kCropThreads) {
+      const AxisCoef c = axis_coef(dx, sc_x, cw, true);
+      xtab[dx] = make_int2(c.s0 * 3, c.w0 | (c.w1 << 16));
+    }
+    if (tid < rows) {
+      const AxisCoef c = axis_coef(y_begin + tid, axis_scale(S, ch), ch, false);
+      yplan[tid][0] = clampi(c.s0, 0, ch - 1);
+      yplan[tid][1] = clampi(c.s0 + 1, 0, ch - 1);
+      yplan[tid][2] = c.w0;
+      yplan[tid][3] = c.w1;
+    }
+  }
+  __syncthreads();
+
+  const int xg = (S + 3) >> 2;
+  const bool vec_ok = (S & 3) == 0;
+  const size_t plane = (size_t)S * S;
+  for (int it = tid; it < rows * xg; it += kCropThreads) {
+    const int j = it / xg;
+    const int x = (it - j * xg) << 2;
+    const int y = y_begin + j;
+    uint32_t px[4][3];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int dx = min(x + k, S - 1);
+      if (empty) {
+        px[k][0] = px[k][1] = px[k][2] = 0;  // mobilenet_preprocess.py:266-267
+      } else if (mode == kResizeCopy) {
+        const uint8_t* s = crop + (size_t)y * row_bytes + dx * 3;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) px[k][c] = __ldg(s + c);
+      } else if (mode == kResizeBox2) {
+        const uint8_t* a = crop + (size_t)(2 * y) * row_bytes + dx * 6;
+        const uint8_t* b = a + row_bytes;
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+          px[k][c] = ((uint32_t)__ldg(a + c) + __ldg(a + c + 3) + __ldg(b + c) + __ldg(b + c + 3) + 2u) >> 2;
+      } else {
+        const int2 e = xtab[dx];
+        const int w0 = e.y & 0xffff, w1 = e.y >> 16;
+        const int b0 = yplan[j][2], b1 = yplan[j][3];
+        const uint8_t* a = crop + (size_t)yplan[j][0] * row_bytes + e.x;
+        const uint8_t* b = crop + (size_t)yplan[j][1] * row_bytes + e.x;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          int h0 = __ldg(a + c) * w0;
+          if (w1) h0 += __ldg(a + c + 3) * w1;
+          int h1 = 0;
+          if (b1) {
+            h1 = __ldg(b + c) * w0;
+            if (w1) h1 += __ldg(b + c + 3) * w1;
+          }
+          px[k][c] = (uint32_t)vresize(h0, h1, b0, b1);
+        }
+      }
+    }
+    float* o = p.out + ((size_t)r * 3) * plane + (size_t)y * S + x;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      if (vec_ok) {
+        st_stream_f4(o + c * plane, lut[c][px[0][c]], lut[c][px[1][c]], lut[c][px[2][c]], lut[c][px[3][c]]);
+      } else {
+        for (int k = 0; k < 4 && x + k < S; ++k) st_stream_f1(o + c * plane + k, lut[c][px[k][c]]);
+      }
+    }
+  }
+}
+
+static int launch_crops(const uint8_t* frames, int src_h, int src_w, const int* rois,
+                        const int* total_dev, int total_host, int roi_slots, int out_size,
+                        const float mean[3], const float stdv[3], float* out, cudaStream_t stream) {
+  if (roi_slots == 0) return IA_OK;
+  CropParams c;
+  c.frames = frames;
+  c.src_h = src_h;
+  c.src_w = src_w;
+  c.rois = rois;
+  c.total_dev = total_dev;
+  c.total_host = total_host;
+  c.roi_slots = roi_slots;
+  c.out_size = out_size;
+  c.groups = (out_size + kCropRows - 1) / kCropRows;
+  for (int i = 0; i < 3; ++i) {
+    c.mean[i] = mean[i];
+    c.stdv[i] = stdv[i];
+  }
+  c.out = out;
+  const long long blocks = (long long)c.groups * roi_slots;
+  IA_RETURN_IF(blocks > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
+  const size_t smem = (size_t)out_size * sizeof(int2);
+  IA_RETURN_IF(smem > 40 * 1024, IA_ERR_UNSUPPORTED);
+  crop_resize_kernel<<<(unsigned)blocks, kCropThreads, smem, stream>>>(c);
+  return launch_status();
+}
+
+// ------------------------------------------------------------------------- small kernels
+__global__ void scale_boxes_kernel(const float* in, int m, int cols, float scale, int pad_w,
+                                   int pad_h, int orig_h, int orig_w, float* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m * cols) return;
+  const int c = i % cols;
+  float v = in[i];
+  if (c < 4) v = (c & 1) ? unletterbox(v, pad_h, scale, orig_h) : unletterbox(v, pad_w, scale, orig_w);
+  out[i] = v;
+}
+
+__global__ void crop_rects_kernel(const float* boxes, int m, int cols, int image_index, int src_h,
+                                  int src_w, int* rois) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const float* b = boxes + (size_t)i * cols;
+  write_roi(rois + (size_t)i * kRoiInts, image_index, b[0], b[1], b[2], b[3], src_h, src_w);
+}
+
+__global__ void normalize_u8_kernel(const uint8_t* in, size_t elems, float m0, float m1, float m2,
+                                    float s0, float s1, float s2, float* out) {
+  __shared__ float lut[3][256];
+  const float mean[3] = {m0, m1, m2}, stdv[3] = {s0, s1, s2};
+  for (int v = threadIdx.x; v < 256; v += blockDim.x) {
+    const float u = __fdiv_rn((float)v, 255.0f);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) lut[c][v] = __fdiv_rn(__fsub_rn(u, mean[c]), stdv[c]);
+  }
+  __syncthreads();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < elems;
+       i += (size_t)gridDim.x * blockDim.x)
+    out[i] = lut[i % 3][in[i]];
+}
+
+}  // namespace ia
+
+extern "C" int ia_scale_boxes(const float* boxes_dev, int m, int cols, float scale, int pad_w,
+                              int pad_h, int orig_h, int orig_w, float* out_dev, void* stream) {
+  IA_RETURN_IF(m < 0 || cols < 4, IA_ERR_INVALID_ARGUMENT);
+  if (m == 0) return IA_OK;
+  IA_RETURN_IF(!boxes_dev || !out_dev, IA_ERR_INVALID_ARGUMENT);
+  const int total = m * cols;
+  ia::scale_boxes_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      boxes_dev, m, cols, scale, pad_w, pad_h, orig_h, orig_w, out_dev);
+  return ia::launch_status();
+}
+
+extern "C" int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int src_h, int src_w,
+                                        const float* dets_dev, const int32_t* count_dev, int max_det,
+                                        float scale, int pad_w, int pad_h, int out_size,
+                                        const float mean[3], const float std[3], float* crops_dev,
+                                        int roi_capacity, int32_t* roi_offsets_dev, int32_t* rois_dev,
+                                        void* stream_) {
+  using namespace ia;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IA_RETURN_IF(n < 0 || src_h < 1 || src_w < 1 || max_det < 1 || out_size < 1 || roi_capacity < 0,
+               IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(!roi_offsets_dev || !mean || !std, IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(n > 0 && (!frames_dev || !dets_dev || !count_dev), IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(roi_capacity > 0 && (!crops_dev || !rois_dev), IA_ERR_INVALID_ARGUMENT);
+  RoiParams a;
+  a.dets = dets_dev;
+  a.count = count_dev;
+  a.n = n;
+  a.max_det = max_det;
+  a.scale = scale;
+  a.pad_w = pad_w;
+  a.pad_h = pad_h;
+  a.src_h = src_h;
+  a.src_w = src_w;
+  a.roi_capacity = roi_capacity;
+  a.offsets = roi_offsets_dev;
+  a.rois = rois_dev;
+  roi_rects_kernel<<<1, kRoiThreads, 0, stream>>>(a);
+  int rc = launch_status();
+  if (rc != IA_OK) return rc;
+  return launch_crops(frames_dev, src_h, src_w, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
+                      out_size, mean, std, crops_dev, stream);
+}
+
+extern "C" int ia_resize_normalize_rois(const uint8_t* frames_dev, int n, int src_h, int src_w,
+                                        const int32_t* rois_dev, int num_rois, int out_size,
+                                        const float mean[3], const float std[3], float* crops_dev,
+                                        void* stream) {
+  IA_RETURN_IF(n < 0 || src_h < 1 || src_w < 1 || num_rois < 0 || out_size < 1, IA_ERR_INVALID_ARGUMENT);
+  if (num_rois == 0) return IA_OK;
+  IA_RETURN_IF(!frames_dev || !rois_dev || !crops_dev || !mean || !std, IA_ERR_INVALID_ARGUMENT);
+  return ia::launch_crops(frames_dev, src_h, src_w, rois_dev, nullptr, num_rois, num_rois, out_size,
+                          mean, std, crops_dev, (cudaStream_t)stream);
+}
+
+extern "C" int ia_extract_crop_rects(const float* boxes_dev, int m, int cols, int image_index,
+                                     int src_h, int src_w, int32_t* rois_dev, void* stream) {
+  IA_RETURN_IF(m < 0 || cols < 4 || src_h < 1 || src_w < 1, IA_ERR_INVALID_ARGUMENT);
+  if (m == 0) return IA_OK;
+  IA_RETURN_IF(!boxes_dev || !rois_dev, IA_ERR_INVALID_ARGUMENT);
+  ia::crop_rects_kernel<<<(m + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      boxes_dev, m, cols, image_index, src_h, src_w, rois_dev);
+  return ia::launch_status();
+}
+
+extern "C" int ia_imagenet_normalize_u8(const uint8_t* image_dev, size_t pixels, const float mean[3],
+                                        const float std[3], float* out_dev, void* stream) {
+  if (pixels == 0) return IA_OK;
+  IA_RETURN_IF(!image_dev || !out_dev || !mean || !std, IA_ERR_INVALID_ARGUMENT);
+  const size_t elems = pixels * 3;
+  size_t blocks = (elems + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  ia::normalize_u8_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      image_dev, elems, mean[0], mean[1], mean[2], std[0], std[1], std[2], out_dev);
+  return ia::launch_status();
+}
+
+extern "C" const char* ia_version(void) { return "ia_b200 0.1.0 sm_100a"; }
+
+extern "C" const char* ia_error_string(int code) {
+  switch (code) {
+    case IA_OK: return "success";
+    case IA_ERR_INVALID_ARGUMENT: return "invalid argument";
+    case IA_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
+    case IA_ERR_UNSUPPORTED: return "unsupported shape or size";
+    case IA_ERR_CAPACITY: return "capacity exceeded";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
+  }
+}

@@ -1,0 +1,98 @@
+"""MobileNetV2 input preparation — same interface as the reference's
+``src/shared/processing/mobilenet_preprocess.py`` (MobileNetPreprocessResult :40-50,
+MobileNetPreprocessor :58-233, extract_crop :236-269).  Resize + ImageNet normalise + CHW
+run in the K4 kernel with the crop as a single whole-image ROI.
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from shared.config import get_controlled_variable
+from shared.processing import _hostio, device as _dev
+from shared.processing.transforms import IMAGENET_MEAN, IMAGENET_STD
+
+_mobilenet_config = get_controlled_variable("preprocessing", "mobilenet")
+MOBILENET_INPUT_SIZE: int = _mobilenet_config["target_size"]
+
+
+@dataclass
+class MobileNetPreprocessResult:
+    """tensor [1,3,S,S] float32 (ImageNet-normalised) and the crop's (height, width)."""
+
+    tensor: np.ndarray
+    original_shape: tuple[int, int]
+
+
+def _whole_image_rois(shapes: list[tuple[int, int]]) -> torch.Tensor:
+    rows = [[i, 0, 0, w, h, 0, 0, 0] for i, (h, w) in enumerate(shapes)]
+    return torch.tensor(rows, dtype=torch.int32)
+
+
+class MobileNetPreprocessor:
+    """Resize a crop to ``input_size`` (bilinear), normalise with the ImageNet statistics,
+    CHW, batch dim."""
+
+    def __init__(self, input_size: int = MOBILENET_INPUT_SIZE, mean: np.ndarray = IMAGENET_MEAN,
+                 std: np.ndarray = IMAGENET_STD) -> None:
+        self.input_size = input_size
+        self.mean = mean
+        self.std = std
+
+    def __call__(self, crop: np.ndarray) -> MobileNetPreprocessResult:
+        return self.preprocess(crop)
+
+    def preprocess(self, crop: np.ndarray) -> MobileNetPreprocessResult:
+        self._validate_input(crop)
+        if crop.dtype != np.uint8:
+            raise NotImplementedError("float32 crops are not on the GPU path yet (DESIGN.md §7)")
+        height, width = crop.shape[0], crop.shape[1]
+        frames = _hostio.to_device(crop)[None]
+        rois = _whole_image_rois([(height, width)]).to(frames.device)
+        # like the reference (mobilenet_preprocess.py:146 -> transforms.py:270) the module-level
+        # ImageNet statistics are applied, not self.mean / self.std
+        tensor = _dev.resize_normalize_rois_cuda(frames, rois, self.input_size, IMAGENET_MEAN, IMAGENET_STD)
+        return MobileNetPreprocessResult(tensor=_hostio.to_host(tensor), original_shape=(height, width))
+
+    def preprocess_batch(self, crops: list[np.ndarray]) -> np.ndarray:
+        if not crops:
+            return np.zeros((0, 3, self.input_size, self.input_size), dtype=np.float32)
+        return np.concatenate([self.preprocess(c).tensor for c in crops], axis=0)
+
+    def _validate_input(self, crop: np.ndarray) -> None:
+        if not isinstance(crop, np.ndarray):
+            raise ValueError(f"Expected numpy array, got {type(crop)}")
+        if crop.ndim != 3:
+            raise ValueError(f"Expected 3D array [H, W, C], got {crop.ndim}D")
+        if crop.shape[2] != 3:
+            raise ValueError(f"Expected 3 channels, got {crop.shape[2]}")
+        if crop.dtype not in (np.uint8, np.float32):
+            raise ValueError(f"Expected uint8 or float32 dtype, got {crop.dtype}")
+        if crop.shape[0] < 1 or crop.shape[1] < 1:
+            raise ValueError(f"Invalid crop dimensions: {crop.shape[:2]}")
+
+    @staticmethod
+    def get_input_shape() -> tuple[int, int, int, int]:
+        return (1, 3, MOBILENET_INPUT_SIZE, MOBILENET_INPUT_SIZE)
+
+    @staticmethod
+    def get_input_dtype() -> np.dtype:
+        return np.dtype(np.float32)
+
+
+def extract_crop(image: np.ndarray, box: np.ndarray) -> np.ndarray:
+    """Copy the region ``box[:4] = [x1, y1, x2, y2]`` (truncated toward zero, clamped to the
+    frame) out of ``image``; an empty region yields ``zeros((1, 1, 3))``.  The rectangle is
+    computed on the device by the code the fused K4 kernel uses; the pixels are a device
+    slice copied back."""
+    height, width = image.shape[:2]
+    row = np.asarray(box[:4], dtype=np.float64).astype(np.float32).reshape(1, 4)
+    frame = _hostio.to_device(image)
+    rect = _hostio.to_host(_dev.extract_crop_rects_cuda(_hostio.to_device(row), height, width))[0]
+    _, x1, y1, x2, y2, empty = (int(v) for v in rect[:6])
+    if empty:
+        return np.zeros((1, 1, 3), dtype=np.uint8)
+    return _hostio.to_host(frame[y1:y2, x1:x2])

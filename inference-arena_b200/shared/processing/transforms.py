@@ -1,0 +1,76 @@
+"""Atomic image transforms — same names and signatures as the reference's
+``src/shared/processing/transforms.py``; arithmetic on the GPU through libia_b200.so.
+
+    letterbox            transforms.py:118-180   -> ia_letterbox_u8
+    scale_boxes          transforms.py:183-230   -> ia_scale_boxes
+    imagenet_normalize   transforms.py:238-272   -> ia_imagenet_normalize_u8
+    load_image(_from_bytes) transforms.py:45-110 -> image decode stays on the host
+                         (libjpeg via cv2; outside the accelerated path)
+"""
+
+from __future__ import annotations
+
+import numpy as np
+
+from shared.config import get_controlled_variable
+from shared.processing import _hostio, device as _dev
+
+_mobilenet_config = get_controlled_variable("preprocessing", "mobilenet")
+IMAGENET_MEAN: np.ndarray = np.array(_mobilenet_config["mean"], dtype=np.float32)
+IMAGENET_STD: np.ndarray = np.array(_mobilenet_config["std"], dtype=np.float32)
+LETTERBOX_COLOR: tuple[int, int, int] = (114, 114, 114)
+
+
+def load_image(image_path: str) -> np.ndarray:
+    """Decode an image file to RGB uint8 [H, W, 3] (host side)."""
+    import cv2
+
+    bgr = cv2.imread(image_path, cv2.IMREAD_COLOR)
+    if bgr is None:
+        raise ValueError(f"Failed to load image: {image_path}")
+    return cv2.cvtColor(bgr, cv2.COLOR_BGR2RGB)
+
+
+def load_image_from_bytes(image_bytes: bytes) -> np.ndarray:
+    """Decode encoded image bytes to RGB uint8 [H, W, 3] (host side)."""
+    import cv2
+
+    if not image_bytes:
+        raise ValueError("Failed to decode image from bytes: empty input")
+    bgr = cv2.imdecode(np.frombuffer(image_bytes, np.uint8), cv2.IMREAD_COLOR)
+    if bgr is None:
+        raise ValueError("Failed to decode image from bytes")
+    return cv2.cvtColor(bgr, cv2.COLOR_BGR2RGB)
+
+
+def letterbox(image: np.ndarray, target_size: int,
+              color: tuple[int, int, int] = LETTERBOX_COLOR) -> tuple[np.ndarray, float, tuple[int, int]]:
+    """Aspect-preserving resize into a ``target_size`` square padded with ``color``.
+    Returns ``(uint8[T,T,3], scale, (pad_w, pad_h))``."""
+    height, width = image.shape[:2]
+    geom = _dev.letterbox_geometry(height, width, target_size)
+    frames = _hostio.to_device(image.astype(np.uint8, copy=False))[None]
+    boxed = _dev.letterbox_batch_cuda(frames, target_size, color)
+    return _hostio.to_host(boxed[0]), geom.scale, geom.padding
+
+
+def scale_boxes(boxes: np.ndarray, scale: float, padding: tuple[int, int],
+                original_shape: tuple[int, int]) -> np.ndarray:
+    """Map ``[N, 4+]`` boxes from letterbox space back to the original frame (input is not
+    modified; columns past the fourth are passed through)."""
+    if boxes.dtype != np.float32:
+        raise NotImplementedError(
+            f"scale_boxes: float32 boxes only on the GPU path, got {boxes.dtype}")
+    if boxes.shape[0] == 0:
+        return boxes.copy()
+    out = _dev.scale_boxes_cuda(_hostio.to_device(boxes), scale, padding, original_shape)
+    return _hostio.to_host(out)
+
+
+def imagenet_normalize(image: np.ndarray) -> np.ndarray:
+    """``(pixel / 255 - mean) / std`` per channel, float32 HWC out."""
+    if image.dtype != np.uint8:
+        raise NotImplementedError(
+            f"imagenet_normalize: uint8 input only on the GPU path, got {image.dtype}")
+    out = _dev.imagenet_normalize_cuda(_hostio.to_device(image), IMAGENET_MEAN, IMAGENET_STD)
+    return _hostio.to_host(out)

@@ -1,0 +1,130 @@
+"""K4 parity (a6..a9): scale_boxes -> extract_crop -> resize 224 -> ImageNet normalise -> CHW
+on the GPU vs the oracle and golden vectors.  Bit-exact float32 tensors and integer rects."""
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import sha
+from oracle import pipeline as O
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def D():
+    from shared.processing import device
+    return device
+
+
+def _dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _oracle_crops(frames, dets, count, geom):
+    out = []
+    for n in range(frames.shape[0]):
+        k = int(count[n])
+        if k == 0:
+            continue
+        boxes = O.scale_boxes(dets[n, :k], geom.scale, (geom.pad_w, geom.pad_h), frames.shape[1:3])
+        for row in boxes:
+            out.append(O.mobilenet_preprocess(O.extract_crop(frames[n], row)))
+    return np.concatenate(out, axis=0) if out else np.zeros((0, 3, 224, 224), np.float32)
+
+
+@pytest.mark.parametrize("h,w", [(480, 640), (1080, 1920), (375, 500)])
+def test_fanout_matches_oracle(D, h, w):
+    n = 12
+    frames = synth.frames(n, h, w, seed=3)
+    dets, count = synth.detections(n, seed=31, kmax=8)
+    geom = D.letterbox_geometry(h, w, 640)
+    crops, offsets, rois = D.crop_batch_cuda(_dev(frames), _dev(dets), _dev(count), geom)
+    torch.cuda.synchronize()
+    offsets = offsets.cpu().numpy()
+    assert np.array_equal(offsets, np.concatenate([[0], np.cumsum(count)]))
+    total = int(offsets[-1])
+    want = _oracle_crops(frames, dets, count, geom)
+    assert np.array_equal(crops[:total].cpu().numpy(), want)
+
+
+def test_edge_rois(D):
+    """Zero-size, 1x1, exact 224 (copy), exact 448 (2x2 box), border-touching and
+    out-of-frame boxes (SURVEY §8d C4 edge list)."""
+    h, w = 480, 640
+    frames = synth.frames(1, h, w, seed=4)
+    boxes = np.array([
+        [10, 90, 10, 200, 0.9, 0], [10, 90, 11.5, 91.2, 0.9, 0], [100, 180, 324, 404, 0.9, 1],
+        [50, 80, 498, 528, 0.9, 2], [0, 80, 640, 560, 0.9, 3], [-50, -50, 30, 130, 0.9, 4],
+        [600, 500, 700, 600, 0.9, 5], [639, 559, 640, 560, 0.9, 6], [700, 700, 800, 800, 0.9, 7],
+        [30.9, 100.9, 31.1, 300.2, 0.8, 8], [5, 85, 9, 535, 0.8, 9], [0, 300, 640, 303, 0.8, 10],
+    ], dtype=np.float32)[None]
+    count = np.array([boxes.shape[1]], dtype=np.int32)
+    geom = D.letterbox_geometry(h, w, 640)
+    crops, offsets, rois = D.crop_batch_cuda(_dev(frames), _dev(boxes), _dev(count), geom)
+    want = _oracle_crops(frames, boxes, count, geom)
+    assert np.array_equal(crops.cpu().numpy(), want)
+    rois = rois.cpu().numpy()
+    scaled = O.scale_boxes(boxes[0], geom.scale, (geom.pad_w, geom.pad_h), (h, w))
+    for r, row in zip(rois, scaled):
+        rect = O.crop_rect(row, h, w)
+        assert (r[5] == 1) == (rect is None)
+        if rect is not None:
+            assert tuple(r[1:5]) == rect
+
+
+def test_mobilenet_golden(D, golden):
+    for case in golden.meta["crops"]:
+        crop = synth.frames(1, case["h"], case["w"], seed=case["seed"])
+        rois = torch.tensor([[0, 0, 0, case["w"], case["h"], 0, 0, 0]], dtype=torch.int32).cuda()
+        t = D.resize_normalize_rois_cuda(_dev(crop), rois).cpu().numpy()
+        assert sha(t) == case["tensor_sha"], case
+
+
+def test_scale_boxes_and_rects_golden(D, golden):
+    boxes = golden["box0_in"]
+    for j, (sc, pad, shape) in enumerate([(1.0, (0, 80), (480, 640)),
+                                          (0.3333333333333333, (0, 140), (1080, 1920)),
+                                          (0.5, (10, 0), (1280, 1240))]):
+        got = D.scale_boxes_cuda(_dev(boxes), sc, pad, shape).cpu().numpy()
+        assert np.array_equal(got, golden[f"box0_scaled{j}"])
+    rects = D.extract_crop_rects_cuda(_dev(boxes), 480, 640).cpu().numpy()
+    for r, shape in zip(rects, golden["box0_crop_shapes"]):
+        got_shape = (1, 1, 3) if r[5] else (r[4] - r[2], r[3] - r[1], 3)
+        assert tuple(shape) == got_shape
+
+
+def test_imagenet_normalize_golden(D, golden):
+    got = D.imagenet_normalize_cuda(_dev(golden["normalize_in"])).cpu().numpy()
+    assert np.array_equal(got, golden["normalize_out"])
+
+
+def test_capacity_and_empty(D):
+    frames = synth.frames(4, 480, 640, seed=6)
+    dets, count = synth.detections(4, seed=32, kmax=8)
+    geom = D.letterbox_geometry(480, 640, 640)
+    crops, offsets, _ = D.crop_batch_cuda(_dev(frames), _dev(dets), _dev(count), geom, roi_capacity=5)
+    want = _oracle_crops(frames, dets, count, geom)
+    assert int(offsets[-1]) == int(count.sum())
+    assert np.array_equal(crops.cpu().numpy(), want[:5])
+    zero = np.zeros_like(count)
+    crops, offsets, _ = D.crop_batch_cuda(_dev(frames), _dev(dets), _dev(zero), geom)
+    assert int(offsets[-1]) == 0
+
+
+def test_full_size_c4(D):
+    """C4 at full size: 512 frames, ~2048 ROIs; offsets are the exclusive scan of counts and a
+    random sample of ROIs equals the oracle."""
+    n = 512
+    frames = synth.frames(n, 480, 640, seed=3)
+    dets, count = synth.detections(n, seed=33, kmax=8)
+    geom = D.letterbox_geometry(480, 640, 640)
+    crops, offsets, rois = D.crop_batch_cuda(_dev(frames), _dev(dets), _dev(count), geom)
+    offsets = offsets.cpu().numpy()
+    assert np.array_equal(offsets, np.concatenate([[0], np.cumsum(count)]))
+    rng = np.random.default_rng(0)
+    for n_i in rng.choice(n, size=24, replace=False):
+        want = _oracle_crops(frames[n_i : n_i + 1], dets[n_i : n_i + 1], count[n_i : n_i + 1], geom)
+        got = crops[offsets[n_i] : offsets[n_i + 1]].cpu().numpy()
+        assert np.array_equal(got, want)

@@ -1,0 +1,143 @@
+"""The numpy-signature drop-in API: same names, argument meaning, ownership and
+error behaviour as the reference's shared.processing / postprocess modules, results equal
+to the oracle.  Mirrors the reference's own tests/shared/test_processing.py cases."""
+
+import numpy as np
+import pytest
+
+from oracle import pipeline as O
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sp():
+    import shared.processing as sp
+    return sp
+
+
+def test_constants(sp):
+    from shared.processing.mobilenet_preprocess import MOBILENET_INPUT_SIZE
+    from shared.processing.transforms import IMAGENET_MEAN, IMAGENET_STD, LETTERBOX_COLOR
+    from shared.processing.yolo_preprocess import YOLO_INPUT_SIZE, YOLO_NORMALIZATION_SCALE
+
+    assert YOLO_INPUT_SIZE == 640 and YOLO_NORMALIZATION_SCALE == 255.0 and MOBILENET_INPUT_SIZE == 224
+    assert LETTERBOX_COLOR == (114, 114, 114)
+    assert IMAGENET_MEAN.dtype == np.float32 and np.array_equal(IMAGENET_MEAN, O.MEAN)
+    assert np.array_equal(IMAGENET_STD, O.STD)
+
+
+def test_yolo_preprocessor(sp):
+    img = synth.frames(1, 1080, 1920, seed=42)[0]
+    res = sp.YOLOPreprocessor()(img)
+    want, scale, pad, shape = O.yolo_preprocess(img)
+    assert res.tensor.shape == (1, 3, 640, 640) and res.tensor.dtype == np.float32
+    assert res.tensor.flags["C_CONTIGUOUS"] and np.array_equal(res.tensor, want)
+    assert res.scale == scale and res.padding == pad and res.original_shape == shape
+    assert sp.YOLOPreprocessor.get_input_shape() == (1, 3, 640, 640)
+    assert sp.YOLOPreprocessor.get_input_dtype() == np.float32
+    boxes = np.array([[320, 320, 400, 400, 0.92, 0], [100, 200, 250, 350, 0.85, 1]], dtype=np.float32)
+    assert np.array_equal(res.scale_boxes_to_original(boxes), O.scale_boxes(boxes, scale, pad, shape))
+    batch = sp.YOLOPreprocessor().preprocess_batch(synth.frames(3, 480, 640, seed=1))
+    assert batch.shape == (3, 3, 640, 640)
+
+
+def test_yolo_validation(sp):
+    p = sp.YOLOPreprocessor()
+    with pytest.raises(ValueError, match="3D array"):
+        p(np.zeros((100, 100), dtype=np.uint8))
+    with pytest.raises(ValueError, match="3 channels"):
+        p(np.zeros((100, 100, 4), dtype=np.uint8))
+    with pytest.raises(ValueError, match="uint8"):
+        p(np.zeros((100, 100, 3), dtype=np.float32))
+    with pytest.raises(ValueError, match="numpy array"):
+        p([[1, 2, 3]])
+
+
+def test_letterbox_and_scale_boxes(sp):
+    img = synth.frames(1, 1920, 1080, seed=44)[0]
+    boxed, scale, pad = sp.letterbox(img, 640)
+    want, wscale, wpad = O.letterbox(img, 640)
+    assert boxed.dtype == np.uint8 and np.array_equal(boxed, want) and scale == wscale and pad == wpad
+    boxes = np.array([[100, 100, 200, 200, 0.95, 0], [300, 150, 450, 350, 0.87, 1]], dtype=np.float32)
+    before = boxes.copy()
+    out = sp.scale_boxes(boxes, 0.5, (10, 20), (480, 640))
+    assert np.array_equal(boxes, before) and np.array_equal(out, O.scale_boxes(boxes, 0.5, (10, 20), (480, 640)))
+
+
+def test_imagenet_normalize(sp):
+    for value in (0, 255):
+        img = np.full((10, 10, 3), value, dtype=np.uint8)
+        got = sp.imagenet_normalize(img)
+        assert got.dtype == np.float32 and got.shape == (10, 10, 3)
+        assert np.allclose(got[0, 0], (value / 255.0 - O.MEAN) / O.STD, rtol=1e-5)
+        assert np.array_equal(got, O.imagenet_normalize(img))
+
+
+def test_mobilenet_preprocessor(sp):
+    from shared.processing.mobilenet_preprocess import extract_crop
+
+    p = sp.MobileNetPreprocessor()
+    for shape, seed in (((100, 150), 45), ((10, 10), 46), ((500, 800), 47)):
+        crop = synth.frames(1, *shape, seed=seed)[0]
+        res = p(crop)
+        assert res.tensor.shape == (1, 3, 224, 224) and res.tensor.flags["C_CONTIGUOUS"]
+        assert res.original_shape == shape and np.array_equal(res.tensor, O.mobilenet_preprocess(crop))
+    assert p.preprocess_batch([]).shape == (0, 3, 224, 224)
+    crops = [synth.frames(1, 50, 60, seed=s)[0] for s in (1, 2, 3)]
+    assert p.preprocess_batch(crops).shape == (3, 3, 224, 224)
+    with pytest.raises(ValueError, match="uint8 or float32"):
+        p(np.zeros((10, 10, 3), dtype=np.int32))
+    with pytest.raises(ValueError, match="Invalid crop dimensions"):
+        p(np.zeros((0, 10, 3), dtype=np.uint8))
+    with pytest.raises(ValueError, match="3 channels"):
+        p(np.zeros((10, 10, 1), dtype=np.uint8))
+
+    image = synth.frames(1, 480, 640, seed=48)[0]
+    for box in ([100, 100, 300, 400, 0.9, 0], [-50, -50, 100, 100], [600, 400, 700, 500], [100, 100, 100, 100],
+                [10.9, 20.9, 50.2, 60.7]):
+        got = extract_crop(image, np.array(box))
+        want = O.extract_crop(image, np.array(box))
+        assert got.shape == want.shape and np.array_equal(got, want)
+    crop = extract_crop(image, np.array([0, 0, 10, 10]))
+    crop[:] = 0
+    assert image[:10, :10].any()  # a copy, not a view
+
+
+def test_postprocess(sp):
+    from shared.processing.postprocess import apply_nms, parse_yolo_output
+
+    head = synth.head_v5(1, seed=1, objects=4)
+    got = parse_yolo_output(head, 0.25, 0.45)
+    want, _ = O.detect_v5(head[0], 0.25, 0.45)
+    assert got.dtype == np.float32 and np.array_equal(got, want)
+    h8 = synth.head_v8_from_v5(synth.head_v5(1, seed=12, anchors=8400))
+    assert np.array_equal(parse_yolo_output(h8, 0.5, 0.45), O.detect_v8(h8[0], 0.5, 0.45)[0])
+    empty = synth.head_v5(1, seed=9, objects=0)
+    out = parse_yolo_output(empty, 0.25, 0.45)
+    assert out.shape == (0, 6) and out.dtype == np.float32
+    boxes, conf, cid = O.decode_v5(head[0])
+    assert apply_nms(boxes, conf, cid, 0.25, 0.45) == O.nms(boxes, conf, cid, 0.25, 0.45)
+    assert apply_nms(boxes, conf, cid, 2.0, 0.45) == []
+    # more detections than the first-pass row budget: wrapper retries with room for all
+    dense = synth.head_v5_dense(1, seed=27, candidates=4000, anchors=6000)
+    want, _ = O.detect_v5(dense[0], 0.25, 0.45)
+    assert np.array_equal(parse_yolo_output(dense, 0.25, 0.45), want)
+
+
+def test_end_to_end_like_reference_pipeline(sp):
+    """The call sequence of monolithic/app/inference.py:161-193 through the drop-in names."""
+    from shared.processing.mobilenet_preprocess import extract_crop
+    from shared.processing.postprocess import parse_yolo_output
+
+    frame = synth.frames(1, 480, 640, seed=0)[0]
+    head = synth.head_v5(1, seed=1, objects=4)
+    want_tensor, want_dets, _, want_orig, want_crops = O.run_image(frame, head[0], 0.25, 0.45)
+    res = sp.YOLOPreprocessor()(frame)
+    dets = parse_yolo_output(head, 0.25, 0.45)
+    orig = res.scale_boxes_to_original(dets)
+    mob = sp.MobileNetPreprocessor()
+    crops = np.concatenate([mob(extract_crop(frame, d)).tensor for d in orig], axis=0)
+    assert np.array_equal(res.tensor, want_tensor) and np.array_equal(dets, want_dets)
+    assert np.array_equal(orig, want_orig) and np.array_equal(crops, want_crops)
