@@ -451,15 +451,15 @@ extern "C" int ia_decode_nms(const float* head_dev, int layout, int n, int ancho
                              void* stream_) {
   using namespace ia;
   cudaStream_t stream = (cudaStream_t)stream_;
-  IA_RETURN_IF(!head_dev || !dets_dev || !keep_dev || !count_dev || !status_dev || !workspace_dev,
-               IA_ERR_INVALID_ARGUMENT);
   IA_RETURN_IF(n < 0 || anchors < 1 || anchors > kMaxAnchors || num_classes < 1 ||
                    num_classes > kMaxClasses || max_det < 1,
                IA_ERR_INVALID_ARGUMENT);
   IA_RETURN_IF(layout != IA_HEAD_LAYOUT_V5 && layout != IA_HEAD_LAYOUT_V8, IA_ERR_INVALID_ARGUMENT);
+  if (n == 0) return IA_OK;
+  IA_RETURN_IF(!head_dev || !dets_dev || !keep_dev || !count_dev || !status_dev || !workspace_dev,
+               IA_ERR_INVALID_ARGUMENT);
   IA_RETURN_IF(((uintptr_t)workspace_dev & 255) != 0 || ((uintptr_t)head_dev & 3) != 0,
                IA_ERR_INVALID_ARGUMENT);
-  if (n == 0) return IA_OK;
   const int cap = max_candidates < 1 || max_candidates > anchors ? anchors : max_candidates;
   Workspace ws = carve(workspace_dev, n, cap);
   IA_RETURN_IF(workspace_bytes < ws.bytes, IA_ERR_WORKSPACE_TOO_SMALL);

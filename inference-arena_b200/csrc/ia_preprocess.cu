@@ -204,9 +204,9 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
 template <bool kOutU8>
 static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, int target,
                             float divisor, uint32_t pad_rgb, void* out, cudaStream_t stream) {
-  IA_RETURN_IF(!frames || !out, IA_ERR_INVALID_ARGUMENT);
   IA_RETURN_IF(n < 0 || src_h < 1 || src_w < 1 || target < 1, IA_ERR_INVALID_ARGUMENT);
   if (n == 0) return IA_OK;
+  IA_RETURN_IF(!frames || !out, IA_ERR_INVALID_ARGUMENT);
   ia_letterbox_geom g;
   int rc = ia_letterbox_geometry(src_h, src_w, target, &g);
   if (rc != IA_OK) return rc;
