@@ -97,6 +97,29 @@ int ia_decode_nms(const float* head_dev, int layout, int n, int anchors, int num
                   float* dets_dev, int32_t* keep_dev, int32_t* count_dev, int32_t* status_dev,
                   void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* ia_decode_nms without a workspace argument and without any allocation.  This entry point
+ * has no counterpart in the reference; it exists for callers that cannot obtain device
+ * memory when they call: processes whose HBM is wholly owned by another allocator (an
+ * inference server's pre-reserved arena, an exhausted MPS/MIG quota) and latency-critical
+ * threads that must stay out of cudaMalloc/cudaFree, which lock and synchronise the device.
+ * The candidate lists live in a fixed 524 544-byte array inside the library (held on every
+ * GPU that loads it until the process exits), which bounds one call to
+ * IA_STATIC_MAX_IMAGES images and IA_STATIC_MAX_CANDIDATES candidates per image:
+ * n above the first, or an effective max_candidates (max_candidates, or `anchors` when it
+ * is < 1 or > anchors) above the second, returns IA_ERR_CAPACITY and launches nothing.
+ * Inputs, outputs and results are exactly those of ia_decode_nms.
+ *   - The first call on each device looks the array's address up (a one-time host-side
+ *     set-up); make that call outside of, and before, any stream capture.
+ *   - All calls on a device share the one array and it keeps the previous call's contents;
+ *     the counters are re-zeroed in stream order by every call.  Two calls whose kernels
+ *     can overlap on the GPU (different streams, no dependency) race on it: serialise them. */
+#define IA_STATIC_MAX_IMAGES 64
+#define IA_STATIC_MAX_CANDIDATES 1024
+int ia_decode_nms_static(const float* head_dev, int layout, int n, int anchors, int num_classes,
+                         float conf_threshold, float iou_threshold, int max_candidates,
+                         int max_det, float* dets_dev, int32_t* keep_dev, int32_t* count_dev,
+                         int32_t* status_dev, void* stream);
+
 /* apply_nms() on already-decoded arrays, postprocess.py:76-160: boxes [m,4] cx,cy,w,h,
  * scores [m], class ids int32 [m] -> keep_dev int32 [max_det] (original indices),
  * count_dev [1], status_dev [1].  Workspace: ia_decode_nms_workspace_bytes(1, m, m). */

@@ -579,3 +579,71 @@ extern "C" int ia_nms(const float* boxes_dev, const float* scores_dev, const int
   nms_kernel<<<1, kNmsThreads, 0, stream>>>(q);
   return launch_status();
 }
+
+// ------------------------------------------------------- allocation-free variant
+// ia_decode_nms_static: the same decode + filter + NMS, but the candidate lists live in a
+// fixed array inside the library image instead of a caller-supplied workspace.  It is meant
+// for callers that have no device memory of their own to lend at call time and must not
+// call an allocator: a serving loop whose HBM is entirely owned by another pool (an
+// inference server's arena, a spent MPS/MIG memory quota), or a latency-critical thread
+// that may never enter cudaMalloc/cudaFree because those serialise against the whole
+// device.  Such a caller still passes the head and the output buffers it already owns.
+#include <mutex>
+
+namespace ia {
+
+constexpr int kStaticMaxImages = IA_STATIC_MAX_IMAGES;
+constexpr int kStaticMaxCandidates = IA_STATIC_MAX_CANDIDATES;
+// counters (one 256-byte block) + one key list of kStaticMaxCandidates per image: 524 544 B
+constexpr size_t kStaticScratchBytes =
+    256 + (size_t)kStaticMaxImages * kStaticMaxCandidates * sizeof(uint64_t);
+
+// Every GPU that loads the library holds these bytes until the process exits.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// In host code `g_static_scratch` is only a handle for the symbol, not an address a kernel
+// can use.  The real device address differs per GPU, so it is looked up once per device,
+// with that device current, and cached.
+static std::mutex g_static_mutex;
+static void* g_static_address[64] = {nullptr};
+
+static int static_scratch_address(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return IA_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (g_static_address[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (ptr == nullptr) return IA_ERR_UNSUPPORTED;
+    g_static_address[dev] = ptr;
+  }
+  *out = g_static_address[dev];
+  return IA_OK;
+}
+
+}  // namespace ia
+
+extern "C" int ia_decode_nms_static(const float* head_dev, int layout, int n, int anchors,
+                                    int num_classes, float conf_threshold, float iou_threshold,
+                                    int max_candidates, int max_det, float* dets_dev,
+                                    int32_t* keep_dev, int32_t* count_dev, int32_t* status_dev,
+                                    void* stream) {
+  using namespace ia;
+  // Sizes first: anything that would not fit the fixed array is refused, never truncated.
+  IA_RETURN_IF(n < 0 || anchors < 1, IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(n > kStaticMaxImages, IA_ERR_CAPACITY);
+  const int cap = max_candidates < 1 || max_candidates > anchors ? anchors : max_candidates;
+  IA_RETURN_IF(cap > kStaticMaxCandidates, IA_ERR_CAPACITY);
+  void* scratch = nullptr;
+  const int rc = static_scratch_address(&scratch);  // first call on a device: one-time look-up
+  if (rc != IA_OK) return rc;
+  // The array still holds the previous call's keys and counters.  Only the counters must
+  // start at zero; ia_decode_nms clears them with a stream-ordered memset before the filter
+  // kernel runs, and every key slot that is read was written by this call first.
+  return ia_decode_nms(head_dev, layout, n, anchors, num_classes, conf_threshold, iou_threshold, cap,
+                       max_det, dets_dev, keep_dev, count_dev, status_dev, scratch,
+                       kStaticScratchBytes, stream);
+}

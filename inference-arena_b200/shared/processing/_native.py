@@ -38,6 +38,8 @@ _SIGNATURES = {
     "ia_decode_nms_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "ia_decode_nms": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_float, c_float, c_int, c_int,
                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "ia_decode_nms_static": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_float, c_float, c_int,
+                                     c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ia_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_float, c_int, c_void_p,
                        c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "ia_scale_boxes": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_int, c_int, c_int,
