@@ -87,7 +87,9 @@ __device__ __forceinline__ void st_stream_f1(float* p, float a) {
 // ------------------------------------------------------------ OpenCV linear coefficients
 constexpr int kCoefOne = 2048;  // INTER_RESIZE_COEF_SCALE (11 bits)
 
-enum ResizeMode : int { kResizeCopy = 0, kResizeBox2 = 1, kResizeLinear = 2 };
+// kResizeGather: a linear resize whose every coefficient pair is (2048, 0) on both axes (an
+// odd integer downscale lands on pixel centres): OpenCV's arithmetic reduces to dst = src[y0][x0].
+enum ResizeMode : int { kResizeCopy = 0, kResizeBox2 = 1, kResizeLinear = 2, kResizeGather = 3 };
 
 __host__ __device__ __forceinline__ int resize_mode(int src_h, int src_w, int dst_h, int dst_w) {
   if (src_h == dst_h && src_w == dst_w) return kResizeCopy;        // resize.cpp: dsize == ssize

@@ -18,8 +18,8 @@
 namespace ia {
 
 constexpr int kRoiThreads = 1024;
-constexpr int kCropThreads = 128;
-constexpr int kCropRows = 8;
+
+
 constexpr int kRoiInts = 8;
 
 // ------------------------------------------------------------------------------ stage A
@@ -106,144 +106,11 @@ __global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams 
   if (tid == 0) p.offsets[p.n] = carry;
 }
 
-// ------------------------------------------------------------------------------ stage B
-struct CropParams {
-  const uint8_t* frames;
-  int src_h, src_w;
-  const int* rois;
-  const int* total_dev;  // number of valid ROIs (device) or null
-  int total_host;        // used when total_dev is null
-  int roi_slots;         // ROIs the grid covers
-  int out_size, groups;
-  float mean[3], stdv[3];
-  float* out;
-};
+}  // namespace ia
 
-__global__ void __launch_bounds__(kCropThreads) crop_resize_kernel(const CropParams p) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  __shared__ float lut[3][256];
-  __shared__ int yplan[kCropRows][4];  // r0, r1, b0, b1
+#include "ia_crop_resize.cuh"  // stage B: crop_resize_kernel, launch_crops
 
-  const int tid = threadIdx.x;
-  const int r = blockIdx.x / p.groups;
-  const int y_begin = (blockIdx.x - r * p.groups) * kCropRows;
-  const int total = p.total_dev ? min(*p.total_dev, p.roi_slots) : p.total_host;
-  if (r >= total) return;
-  const int S = p.out_size;
-  const int rows = min(kCropRows, S - y_begin);
-  int2* xtab = reinterpret_cast<int2*>(smem);
-
-  const int* roi = p.rois + (size_t)r * kRoiInts;
-  const int img = roi[0];
-  const int empty = roi[5];
-  const int rx1 = roi[1], ry1 = roi[2];
-  const int cw = empty ? 1 : roi[3] - roi[1];
-  const int ch = empty ? 1 : roi[4] - roi[2];
-  const int mode = resize_mode(ch, cw, S, S);
-  const size_t row_bytes = (size_t)p.src_w * 3;
-  const uint8_t* crop = p.frames + (size_t)img * p.src_h * row_bytes + (size_t)ry1 * row_bytes + (size_t)rx1 * 3;
-
-  for (int v = tid; v < 256; v += kCropThreads) {
-    const float u = __fdiv_rn((float)v, 255.0f);  // transforms.py:263
-#pragma unroll
-    for (int c = 0; c < 3; ++c) lut[c][v] = __fdiv_rn(__fsub_rn(u, p.mean[c]), p.stdv[c]);  // :270
-  }
-  if (mode == kResizeLinear) {
-    const double sc_x = axis_scale(S, cw);
-    for (int dx = tid; dx < S; dx += kCropThreads) {
-      const AxisCoef c = axis_coef(dx, sc_x, cw, true);
-      xtab[dx] = make_int2(c.s0 * 3, c.w0 | (c.w1 << 16));
-    }
-    if (tid < rows) {
-      const AxisCoef c = axis_coef(y_begin + tid, axis_scale(S, ch), ch, false);
-      yplan[tid][0] = clampi(c.s0, 0, ch - 1);
-      yplan[tid][1] = clampi(c.s0 + 1, 0, ch - 1);
-      yplan[tid][2] = c.w0;
-      yplan[tid][3] = c.w1;
-    }
-  }
-  __syncthreads();
-
-  const int xg = (S + 3) >> 2;
-  const bool vec_ok = (S & 3) == 0;
-  const size_t plane = (size_t)S * S;
-  for (int it = tid; it < rows * xg; it += kCropThreads) {
-    const int j = it / xg;
-    const int x = (it - j * xg) << 2;
-    const int y = y_begin + j;
-    uint32_t px[4][3];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int dx = min(x + k, S - 1);
-      if (empty) {
-        px[k][0] = px[k][1] = px[k][2] = 0;  // mobilenet_preprocess.py:266-267
-      } else if (mode == kResizeCopy) {
-        const uint8_t* s = crop + (size_t)y * row_bytes + dx * 3;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) px[k][c] = __ldg(s + c);
-      } else if (mode == kResizeBox2) {
-        const uint8_t* a = crop + (size_t)(2 * y) * row_bytes + dx * 6;
-        const uint8_t* b = a + row_bytes;
-#pragma unroll
-        for (int c = 0; c < 3; ++c)
-          px[k][c] = ((uint32_t)__ldg(a + c) + __ldg(a + c + 3) + __ldg(b + c) + __ldg(b + c + 3) + 2u) >> 2;
-      } else {
-        const int2 e = xtab[dx];
-        const int w0 = e.y & 0xffff, w1 = e.y >> 16;
-        const int b0 = yplan[j][2], b1 = yplan[j][3];
-        const uint8_t* a = crop + (size_t)yplan[j][0] * row_bytes + e.x;
-        const uint8_t* b = crop + (size_t)yplan[j][1] * row_bytes + e.x;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          int h0 = __ldg(a + c) * w0;
-          if (w1) h0 += __ldg(a + c + 3) * w1;
-          int h1 = 0;
-          if (b1) {
-            h1 = __ldg(b + c) * w0;
-            if (w1) h1 += __ldg(b + c + 3) * w1;
-          }
-          px[k][c] = (uint32_t)vresize(h0, h1, b0, b1);
-        }
-      }
-    }
-    float* o = p.out + ((size_t)r * 3) * plane + (size_t)y * S + x;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      if (vec_ok) {
-        st_stream_f4(o + c * plane, lut[c][px[0][c]], lut[c][px[1][c]], lut[c][px[2][c]], lut[c][px[3][c]]);
-      } else {
-        for (int k = 0; k < 4 && x + k < S; ++k) st_stream_f1(o + c * plane + k, lut[c][px[k][c]]);
-      }
-    }
-  }
-}
-
-static int launch_crops(const uint8_t* frames, int src_h, int src_w, const int* rois,
-                        const int* total_dev, int total_host, int roi_slots, int out_size,
-                        const float mean[3], const float stdv[3], float* out, cudaStream_t stream) {
-  if (roi_slots == 0) return IA_OK;
-  CropParams c;
-  c.frames = frames;
-  c.src_h = src_h;
-  c.src_w = src_w;
-  c.rois = rois;
-  c.total_dev = total_dev;
-  c.total_host = total_host;
-  c.roi_slots = roi_slots;
-  c.out_size = out_size;
-  c.groups = (out_size + kCropRows - 1) / kCropRows;
-  for (int i = 0; i < 3; ++i) {
-    c.mean[i] = mean[i];
-    c.stdv[i] = stdv[i];
-  }
-  c.out = out;
-  const long long blocks = (long long)c.groups * roi_slots;
-  IA_RETURN_IF(blocks > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
-  const size_t smem = (size_t)out_size * sizeof(int2);
-  IA_RETURN_IF(smem > 40 * 1024, IA_ERR_UNSUPPORTED);
-  crop_resize_kernel<<<(unsigned)blocks, kCropThreads, smem, stream>>>(c);
-  return launch_status();
-}
+namespace ia {
 
 // ------------------------------------------------------------------------- small kernels
 __global__ void scale_boxes_kernel(const float* in, int m, int cols, float scale, int pad_w,
@@ -321,7 +188,7 @@ extern "C" int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int sr
   roi_rects_kernel<<<1, kRoiThreads, 0, stream>>>(a);
   int rc = launch_status();
   if (rc != IA_OK) return rc;
-  return launch_crops(frames_dev, src_h, src_w, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
+  return launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
                       out_size, mean, std, crops_dev, stream);
 }
 
@@ -332,7 +199,7 @@ extern "C" int ia_resize_normalize_rois(const uint8_t* frames_dev, int n, int sr
   IA_RETURN_IF(n < 0 || src_h < 1 || src_w < 1 || num_rois < 0 || out_size < 1, IA_ERR_INVALID_ARGUMENT);
   if (num_rois == 0) return IA_OK;
   IA_RETURN_IF(!frames_dev || !rois_dev || !crops_dev || !mean || !std, IA_ERR_INVALID_ARGUMENT);
-  return ia::launch_crops(frames_dev, src_h, src_w, rois_dev, nullptr, num_rois, num_rois, out_size,
+  return ia::launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, rois_dev, nullptr, num_rois, num_rois, out_size,
                           mean, std, crops_dev, (cudaStream_t)stream);
 }
 

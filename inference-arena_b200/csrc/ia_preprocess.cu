@@ -3,21 +3,32 @@
 // Replaces YOLOPreprocessor.preprocess (reference src/shared/processing/
 // yolo_preprocess.py:128-174) and letterbox (transforms.py:118-180) for a batch of
 // equally-sized uint8 HWC frames.  One CTA produces a group of output rows of one image:
-//   1. warp 0 stages the source rows those output rows need into shared memory with 1-D
-//      bulk async copies (cp.async.bulk -> TMA engine, completion on an mbarrier); the
-//      <= 15 unaligned bytes at either end of a segment are copied by the same lanes;
+//   1. warp 0 works out which source rows those output rows need (OpenCV's yofs/beta
+//      table), drops duplicates and zero-weight rows, and stages each distinct row into
+//      shared memory with a 1-D bulk async copy (cp.async.bulk -> TMA engine, completion on
+//      an mbarrier); the <= 15 unaligned bytes at either end of a row are copied by the lane;
 //   2. meanwhile the other warps build the u8 -> float LUT (exact float32 division, same
-//      as numpy's `astype(float32) / 255.0`) and the OpenCV x-coefficient table;
+//      as numpy's `astype(float32) / 255.0`; 8 copies across banks) and the x-coefficient
+//      table;
 //   3. every thread then produces 4 consecutive output pixels: 8-bit fixed-point bilinear
-//      (bit-identical to cv2.resize INTER_LINEAR), LUT, three coalesced 128-bit stores —
-//      one per colour plane.
+//      (bit-identical to cv2.resize INTER_LINEAR), LUT, three coalesced 128-bit streaming
+//      stores — one per colour plane.
+// The host evaluates the same coefficient tables to size the staging buffer exactly (a 3x
+// downscale of 1080p needs ONE source row per output row), which sets the occupancy.
 // HBM traffic = source rows actually needed + the output, each once.
+#include <math.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
 #include "ia_common.cuh"
 
 namespace ia {
 
 constexpr int kPreThreads = 256;
 constexpr int kPreMaxRows = 8;
+constexpr int kPreLutRep = 8;
 
 struct PreParams {
   const uint8_t* frames;
@@ -26,32 +37,83 @@ struct PreParams {
   int new_h, new_w, pad_h, pad_w;
   int rows_per_cta, groups;
   int slot_bytes;  // shared-memory bytes reserved per staged source row (16-byte multiple)
+  int slots_cap;   // staged rows a CTA has room for (computed exactly by the host)
   float divisor;
   double sc_x, sc_y;
   uint32_t pad_rgb;  // r | g << 8 | b << 16
 };
 
 struct RowPlan {
-  int image_row;  // 0: padding row
-  int off0, off1; // shared-memory byte offsets of the two staged source rows
-  int b0, b1;     // vertical coefficients
+  int image_row;   // 0: padding row
+  int off0, off1;  // shared-memory byte offsets of the two staged source rows
+  int b0, b1;      // vertical coefficients
 };
+
+// Host twin of axis_coef (ia_common.cuh): plain IEEE double/float operations, one rounding
+// per step (volatile keeps the host compiler from contracting or reassociating).
+static AxisCoef axis_coef_host(int i, double sc, int src, bool zero_frac_at_border) {
+  volatile double t = (double)i + 0.5;
+  t = t * sc;
+  t = t - 0.5;
+  volatile float f = (float)t;
+  int s0 = (int)floorf(f);
+  f = f - (float)s0;
+  if (zero_frac_at_border) {
+    if (s0 < 0) s0 = 0, f = 0.f;
+    if (s0 >= src - 1) s0 = src - 1, f = 0.f;
+  }
+  volatile float w1 = f * (float)kCoefOne;
+  volatile float w0 = 1.f - f;
+  w0 = w0 * (float)kCoefOne;
+  AxisCoef c;
+  c.s0 = s0;
+  c.w1 = (int)lrintf(w1);
+  c.w0 = (int)lrintf(w0);
+  return c;
+}
+
+// Source rows (r0, r1; -1 = not needed) and weights of letterboxed output row y.
+__host__ __device__ inline bool row_sources(int mode, int dy, int new_h, int src_h, double sc_y,
+                                            int& r0, int& r1, int& b0, int& b1) {
+  r0 = r1 = -1;
+  b0 = kCoefOne;
+  b1 = 0;
+  if (dy < 0 || dy >= new_h) return false;
+  if (mode == kResizeCopy) {
+    r0 = dy;
+  } else if (mode == kResizeBox2) {
+    r0 = 2 * dy;
+    r1 = 2 * dy + 1;
+    b0 = b1 = kCoefOne / 2;
+  } else {
+#ifdef __CUDA_ARCH__
+    const AxisCoef c = axis_coef(dy, sc_y, src_h, false);
+#else
+    const AxisCoef c = axis_coef_host(dy, sc_y, src_h, false);
+#endif
+    b0 = c.w0;
+    b1 = c.w1;
+    r0 = c.s0 < 0 ? 0 : (c.s0 > src_h - 1 ? src_h - 1 : c.s0);
+    if (c.w1 != 0) r1 = c.s0 + 1 < 0 ? 0 : (c.s0 + 1 > src_h - 1 ? src_h - 1 : c.s0 + 1);
+  }
+  return true;
+}
 
 template <bool kOutU8, int kMode>
 __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ float lut[256];
+  __shared__ float lut[kOutU8 ? 1 : 256 * kPreLutRep];
   __shared__ RowPlan plan[kPreMaxRows];
-  __shared__ int seg_row[2 * kPreMaxRows];  // source row per staging segment, -1 = none
+  __shared__ int seg_row[2 * kPreMaxRows];  // source row per (output row, tap), -1 = none
   __shared__ __align__(8) uint64_t bar;
 
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
   const int img = blockIdx.x / p.groups;
   const int y_begin = (blockIdx.x % p.groups) * p.rows_per_cta;
   const int rows = min(p.rows_per_cta, p.target - y_begin);
   const uint32_t row_bytes = (uint32_t)p.src_w * 3u;
   const uint8_t* frame = p.frames + (size_t)img * p.src_h * row_bytes;
-  int2* xtab = reinterpret_cast<int2*>(smem + (size_t)2 * p.rows_per_cta * p.slot_bytes);
+  int2* xtab = reinterpret_cast<int2*>(smem + (size_t)p.slots_cap * p.slot_bytes);
 
   if (tid == 0) {
     mbar_init(&bar, 1);
@@ -59,46 +121,33 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
   }
   // ---- per-row plan: which source rows, which vertical weights -------------------
   if (tid < rows) {
-    const int dy = y_begin + tid - p.pad_h;
+    int r0, r1, b0, b1;
     RowPlan rp;
-    rp.image_row = (dy >= 0 && dy < p.new_h) ? 1 : 0;
+    rp.image_row = row_sources(kMode, y_begin + tid - p.pad_h, p.new_h, p.src_h, p.sc_y, r0, r1, b0, b1) ? 1 : 0;
     rp.off0 = rp.off1 = 0;
-    rp.b0 = kCoefOne;
-    rp.b1 = 0;
-    int r0 = -1, r1 = -1;
-    if (rp.image_row) {
-      if (kMode == kResizeCopy) {
-        r0 = dy;
-      } else if (kMode == kResizeBox2) {
-        r0 = 2 * dy;
-        r1 = 2 * dy + 1;
-      } else {
-        const AxisCoef c = axis_coef(dy, p.sc_y, p.src_h, false);
-        rp.b0 = c.w0;
-        rp.b1 = c.w1;
-        r0 = clampi(c.s0, 0, p.src_h - 1);
-        if (c.w1 != 0) r1 = clampi(c.s0 + 1, 0, p.src_h - 1);
-      }
-    }
-    const uint32_t mis0 = r0 >= 0 ? (uint32_t)((uintptr_t)(frame + (size_t)r0 * row_bytes) & 15) : 0;
-    const uint32_t mis1 = r1 >= 0 ? (uint32_t)((uintptr_t)(frame + (size_t)r1 * row_bytes) & 15) : 0;
-    rp.off0 = (2 * tid) * p.slot_bytes + mis0;
-    rp.off1 = (2 * tid + 1) * p.slot_bytes + mis1;
+    rp.b0 = b0;
+    rp.b1 = b1;
     plan[tid] = rp;
     seg_row[2 * tid] = r0;
     seg_row[2 * tid + 1] = r1;
   }
   __syncthreads();
 
-  // ---- stage source rows: bulk async copy of the 16-byte aligned body ------------
+  // ---- stage the distinct source rows: bulk async copy of the 16-byte aligned body -------
   if (tid < 32) {
-    const uint8_t* g = nullptr;
-    uint8_t* s = nullptr;
+    const int j = lane >> 1, tap = lane & 1;
+    const int row = (j < rows) ? seg_row[lane] : -1;
+    const unsigned same = __match_any_sync(0xffffffffu, row);
+    const int leader = __ffs(same) - 1;
+    const bool copy = (leader == lane) && row >= 0;
+    const unsigned leaders = __ballot_sync(0xffffffffu, copy);
+    const int slot = __popc(leaders & ((1u << leader) - 1u));
+    if (row >= 0 && slot >= p.slots_cap) __trap();  // host and device tables disagree: never expected
+    const uint8_t* g = frame + (size_t)max(row, 0) * row_bytes;
+    const uint32_t mis = (uint32_t)((uintptr_t)g & 15);
+    const int off = slot * p.slot_bytes + (int)mis;
     uint32_t head = 0, body = 0, tail = 0;
-    if (tid < 2 * rows && seg_row[tid] >= 0) {
-      g = frame + (size_t)seg_row[tid] * row_bytes;
-      const uint32_t mis = (uint32_t)((uintptr_t)g & 15);
-      s = smem + (size_t)tid * p.slot_bytes + mis;
+    if (copy) {
       head = min(row_bytes, (16u - mis) & 15u);
       body = (row_bytes - head) & ~15u;
       tail = row_bytes - head - body;
@@ -106,18 +155,26 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
     uint32_t total = body;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-    if (tid == 0) mbar_expect_tx(&bar, total);
+    if (lane == 0) mbar_expect_tx(&bar, total);
     __syncwarp();
-    if (body) bulk_g2s(s + head, g + head, body, &bar);
-    for (uint32_t i = 0; i < head; ++i) s[i] = g[i];
-    for (uint32_t i = 0; i < tail; ++i) s[head + body + i] = g[head + body + i];
+    if (copy) {
+      uint8_t* s = smem + off;
+      if (body) bulk_g2s(s + head, g + head, body, &bar);
+      for (uint32_t i = 0; i < head; ++i) s[i] = g[i];
+      for (uint32_t i = 0; i < tail; ++i) s[head + body + i] = g[head + body + i];
+    }
+    if (j < rows && row >= 0) {
+      if (tap == 0) plan[j].off0 = off;
+      else plan[j].off1 = off;
+    }
   }
 
   // ---- tables ---------------------------------------------------------------------
   if (!kOutU8) {
-    for (int v = tid; v < 256; v += kPreThreads) lut[v] = __fdiv_rn((float)v, p.divisor);
+    for (int i = tid; i < 256 * kPreLutRep; i += kPreThreads)
+      lut[i] = __fdiv_rn((float)(i / kPreLutRep), p.divisor);
   }
-  if (kMode == kResizeLinear) {
+  if (kMode == kResizeLinear || kMode == kResizeGather) {
     for (int dx = tid; dx < p.new_w; dx += kPreThreads) {
       const AxisCoef c = axis_coef(dx, p.sc_x, p.src_w, true);
       xtab[dx] = make_int2(c.s0 * 3, c.w0 | (c.w1 << 16));
@@ -131,10 +188,14 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
   const int xg = (T + 3) >> 2;
   const uint32_t pr = p.pad_rgb & 0xff, pg = (p.pad_rgb >> 8) & 0xff, pb = (p.pad_rgb >> 16) & 0xff;
   const bool vec_ok = (T & 3) == 0;
+  const float* l = lut + (kOutU8 ? 0 : (lane & (kPreLutRep - 1)));
 
-  for (int it = tid; it < rows * xg; it += kPreThreads) {
-    const int j = it / xg;
-    const int x = (it - j * xg) << 2;
+  // (row j, pixel group gx) of item `tid`, then advanced by kPreThreads items per iteration
+  int j = tid / xg, gx = tid - j * xg;
+  const int dj = kPreThreads / xg, dg = kPreThreads - dj * xg;
+  for (int it = tid; it < rows * xg; it += kPreThreads, j += dj, gx += dg) {
+    if (gx >= xg) gx -= xg, ++j;
+    const int x = gx << 2;
     const int y = y_begin + j;
     const RowPlan rp = plan[j];
     const uint8_t* p0 = smem + rp.off0;
@@ -157,6 +218,11 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
         const uint8_t* b = p1 + dx * 6;
 #pragma unroll
         for (int c = 0; c < 3; ++c) px[k][c] = ((uint32_t)a[c] + a[c + 3] + b[c] + b[c + 3] + 2u) >> 2;
+      } else if (kMode == kResizeGather) {
+        const uint8_t* s = p0 + xtab[dx].x;
+        px[k][0] = s[0];
+        px[k][1] = s[1];
+        px[k][2] = s[2];
       } else {
         const int2 e = xtab[dx];
         const int w0 = e.y & 0xffff, w1 = e.y >> 16;
@@ -164,13 +230,10 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
         const uint8_t* b = p1 + e.x;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          int h0 = a[c] * w0;
-          if (w1) h0 += a[c + 3] * w1;
-          int h1 = 0;
-          if (rp.b1) {
-            h1 = b[c] * w0;
-            if (w1) h1 += b[c + 3] * w1;
-          }
+          // branch-free: a zero weight multiplies a byte that is always inside the staging
+          // buffer (every slot has 16 spare bytes) by 0
+          const int h0 = a[c] * w0 + a[c + 3] * w1;
+          const int h1 = b[c] * w0 + b[c + 3] * w1;
           px[k][c] = (uint32_t)vresize(h0, h1, rp.b0, rp.b1);
         }
       }
@@ -192,13 +255,35 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         if (vec_ok) {
-          st_stream_f4(o + c * plane, lut[px[0][c]], lut[px[1][c]], lut[px[2][c]], lut[px[3][c]]);
+          st_stream_f4(o + c * plane, l[px[0][c] * kPreLutRep], l[px[1][c] * kPreLutRep],
+                       l[px[2][c] * kPreLutRep], l[px[3][c] * kPreLutRep]);
         } else {
-          for (int k = 0; k < 4 && x + k < T; ++k) st_stream_f1(o + c * plane + k, lut[px[k][c]]);
+          for (int k = 0; k < 4 && x + k < T; ++k) st_stream_f1(o + c * plane + k, l[px[k][c] * kPreLutRep]);
         }
       }
     }
   }
+}
+
+// Distinct source rows the busiest CTA has to stage when each CTA owns `rows` output rows.
+static int max_distinct_rows(int mode, int rows, const ia_letterbox_geom& g, double sc_y) {
+  int worst = 1;
+  for (int y0 = 0; y0 < g.target; y0 += rows) {
+    int seen[2 * kPreMaxRows];
+    int n = 0;
+    for (int j = 0; j < rows && y0 + j < g.target; ++j) {
+      int r[2], b0, b1;
+      row_sources(mode, y0 + j - g.pad_h, g.new_h, g.src_h, sc_y, r[0], r[1], b0, b1);
+      for (int t = 0; t < 2; ++t) {
+        if (r[t] < 0) continue;
+        bool dup = false;
+        for (int k = 0; k < n; ++k) dup |= seen[k] == r[t];
+        if (!dup) seen[n++] = r[t];
+      }
+    }
+    if (n > worst) worst = n;
+  }
+  return worst;
 }
 
 template <bool kOutU8>
@@ -226,16 +311,42 @@ static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, 
   p.sc_x = axis_scale(g.new_w, src_w);
   p.sc_y = axis_scale(g.new_h, src_h);
   p.pad_rgb = pad_rgb;
-  p.slot_bytes = (((src_w * 3 + 15) & ~15) + 16);
-  const int mode = resize_mode(src_h, src_w, g.new_h, g.new_w);
-  const size_t xtab_bytes = (size_t)g.new_w * sizeof(int2);
-  const size_t budget = 96 * 1024;
-  int rows = kPreMaxRows;
-  while (rows > 1 && (size_t)2 * rows * p.slot_bytes + xtab_bytes > budget) rows >>= 1;
-  const size_t smem = (size_t)2 * rows * p.slot_bytes + xtab_bytes;
-  IA_RETURN_IF(smem > 220 * 1024, IA_ERR_UNSUPPORTED);
-  IA_RETURN_IF((size_t)rows * 2 * src_w * 3 >= (1u << 20), IA_ERR_UNSUPPORTED);  // mbarrier tx range
+  p.slot_bytes = (((src_w * 3 + 15) & ~15) + 32);  // row + misalignment + branch-free over-read
+  int mode = resize_mode(src_h, src_w, g.new_h, g.new_w);
+  const size_t xtab_bytes = mode == kResizeLinear ? (size_t)g.new_w * sizeof(int2) : 0;
+  // rows per CTA: the largest group whose staging buffer leaves room for >= 6 CTAs per SM.
+  // The table walk costs tens of microseconds on the host, so it is done once per geometry.
+  int rows = kPreMaxRows, slots = 0;
+  {
+    static std::mutex mu;
+    static std::map<std::tuple<int, int, int>, std::tuple<int, int, int>> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    const auto key = std::make_tuple(src_h, src_w, target);
+    auto it = cache.find(key);
+    if (it == cache.end()) {
+      if (mode == kResizeLinear) {  // all second coefficients zero on both axes -> pure gather
+        bool gather = true;
+        for (int x = 0; x < g.new_w && gather; ++x) gather = axis_coef_host(x, p.sc_x, src_w, true).w1 == 0;
+        for (int y = 0; y < g.new_h && gather; ++y) gather = axis_coef_host(y, p.sc_y, src_h, false).w1 == 0;
+        if (gather) mode = kResizeGather;
+      }
+      for (;; rows >>= 1) {
+        slots = max_distinct_rows(mode, rows, g, p.sc_y);
+        if (rows == 1 || (size_t)slots * p.slot_bytes + xtab_bytes <= 28 * 1024) break;
+      }
+      if (cache.size() > 256) cache.clear();
+      cache[key] = std::make_tuple(rows, slots, mode);
+    } else {
+      rows = std::get<0>(it->second);
+      slots = std::get<1>(it->second);
+      mode = std::get<2>(it->second);
+    }
+  }
+  const size_t smem = (size_t)slots * p.slot_bytes + xtab_bytes;
+  IA_RETURN_IF(smem > 200 * 1024, IA_ERR_UNSUPPORTED);
+  IA_RETURN_IF((size_t)slots * src_w * 3 >= (1u << 20), IA_ERR_UNSUPPORTED);  // mbarrier tx range
   p.rows_per_cta = rows;
+  p.slots_cap = slots;
   p.groups = (target + rows - 1) / rows;
   const long long blocks = (long long)p.groups * n;
   IA_RETURN_IF(blocks > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
@@ -244,6 +355,7 @@ static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, 
   switch (mode) {
     case kResizeCopy: kernel = letterbox_kernel<kOutU8, kResizeCopy>; break;
     case kResizeBox2: kernel = letterbox_kernel<kOutU8, kResizeBox2>; break;
+    case kResizeGather: kernel = letterbox_kernel<kOutU8, kResizeGather>; break;
     default: kernel = letterbox_kernel<kOutU8, kResizeLinear>; break;
   }
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
