@@ -1,20 +1,25 @@
-// ia_crop_resize.cuh — K4 stage B: ROI resize + normalise + CHW, double-buffered row staging.
+// ia_crop_resize.cuh — K4 stage B: ROI resize + normalise + CHW.
+// Warp-specialised, double-buffered, persistent.
 //
-// Work is a stream of steps; a step is a sub-band (<= 16 output rows, sized to the staging
+// Work is a stream of steps; a step is a sub-band (<= 16 output rows, sized to one staging
 // buffer) of one ROI.  CTAs are persistent (grid = SMs x resident CTAs) and stride over the
-// (ROI, band) items; the ROI total is read from device memory, so nothing returns to the host
-// between NMS and here.  Per step:
-//   issue   (warp 0, one step AHEAD of the math): lane (row j, tap) evaluates OpenCV's
-//           yofs/beta entry, duplicates are removed with __match_any_sync, and each distinct
-//           crop row segment is pulled into the idle staging buffer with one 1-D bulk async
-//           copy (TMA engine, mbarrier completion) of its 16-byte-aligned superset, clamped
-//           to the frame buffer (bytes a clamp cuts off are copied by the lane);
-//   compute (all warps, warp per output row): 4 consecutive pixels per lane — branch-free
-//           11-bit fixed-point bilinear on bytes from shared memory (bit-identical to
-//           cv2.resize INTER_LINEAR; copy and the exact-2x box average use the same arithmetic
-//           with tables a0=b0=2048 resp. a0=a1=b0=b1=1024, which reduce to the identity and to
-//           (p00+p01+p10+p11+2)>>2), the ((v/255 - mean)/std) LUT replicated 8x across banks,
-//           three 128-bit streaming plane stores.
+// (ROI, band) items; the ROI total is read from device memory, so nothing returns to the
+// host between NMS and here.  A CTA is 8 consumer warps + 1 producer warp, coupled only by
+// mbarriers (full[2] / empty[2]) — no CTA-wide barrier in the loop:
+//   producer: lane (row j, tap) evaluates OpenCV's yofs/beta entry, duplicates are removed
+//           with __match_any_sync, the row plan is published, and each distinct crop row
+//           segment is pulled into the free staging buffer with one 1-D bulk async copy (TMA
+//           engine, complete_tx on full[buf]) of its 16-byte-aligned superset, clamped to the
+//           frame buffer (bytes a clamp cuts off are copied by the lane).  It runs up to two
+//           steps ahead of the math.
+//   consumers: 4 consecutive pixels x 3 channels per lane.  The 6 source bytes of a pixel's
+//           two taps come from three aligned 32-bit shared loads + a funnel shift; a PRMT
+//           pairs (p[c], p[c+3]) and one IDP.2A does p0*a0 + p1*a1 against the packed
+//           coefficient pair — OpenCV's 11-bit fixed point, bit-identical to cv2.resize
+//           INTER_LINEAR (copy and the exact-2x box average use the same arithmetic with
+//           tables a0=b0=2048 resp. a0=a1=b0=b1=1024, which reduce to the identity and to
+//           (p00+p01+p10+p11+2)>>2).  Then the ((v/255 - mean)/std) LUT, replicated 8x across
+//           banks, and three 128-bit streaming plane stores.
 // The global side sees only wide, fully used requests; byte gathers hit shared memory.
 #pragma once
 
@@ -22,8 +27,8 @@
 
 namespace ia {
 
-constexpr int kCropThreads = 256;
-constexpr int kCropWarps = kCropThreads / 32;
+constexpr int kCropConsumers = 256;
+constexpr int kCropThreads = kCropConsumers + 32;
 constexpr int kBandRows = 16;
 constexpr int kLutRep = 8;  // copies of each LUT entry, one per (lane & 7): fewer bank conflicts
 
@@ -42,11 +47,11 @@ struct CropParams {
 };
 
 struct YPlan {
-  int off0, off1;  // shared-memory byte offsets (within a staging buffer) of the two crop rows
+  int off0, off1;  // byte offsets (within a staging buffer) of crop byte 0 of the two rows
   int b0, b1;
 };
 
-// Position in the step stream; advanced identically by every thread of the CTA.
+// Position in the step stream; producer and consumers advance their own copy identically.
 struct Cursor {
   int item, sb, nsub, sub_rows;
   int r, y_band, rows;  // ROI index, first output row of the band, rows in the band
@@ -82,26 +87,13 @@ __device__ __forceinline__ bool advance(Cursor& c, const CropParams& p, int item
   return load_item(c, p, c.item + (int)gridDim.x, items);
 }
 
-// Source rows / weights of output row y of the crop (OpenCV's vertical table).
-__device__ __forceinline__ void y_entry(const Cursor& c, int S, int y, int tap, int& row, int& b0, int& b1) {
-  b0 = kCoefOne;
-  b1 = 0;
-  if (c.mode == kResizeCopy) {
-    row = tap ? -1 : y;
-  } else if (c.mode == kResizeBox2) {
-    row = 2 * y + tap;
-    b0 = b1 = kCoefOne / 2;
-  } else {
-    const AxisCoef k = axis_coef(y, axis_scale(S, c.ch), c.ch, false);
-    b0 = k.w0;
-    b1 = k.w1;
-    row = tap ? (k.w1 != 0 ? clampi(k.s0 + 1, 0, c.ch - 1) : -1) : clampi(k.s0, 0, c.ch - 1);
+// Producer warp: plan + stage the crop rows of step `c`; arrives on `full`.
+__device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& p, double sc_y,
+                                             uint8_t* stage, YPlan* plan, uint64_t* full, int lane) {
+  if (c.empty) {  // nothing to stage; keep the barrier protocol uniform
+    if (lane == 0) mbar_expect_tx(full, 0);
+    return;
   }
-}
-
-// Warp 0: stage the crop rows of step `c` into `stage`, publish the row plan.
-__device__ __forceinline__ void issue_step(const Cursor& c, const CropParams& p, uint8_t* stage,
-                                           YPlan* plan, uint64_t* bar, int lane) {
   const int S = p.out_size;
   const size_t row_bytes = (size_t)p.src_w * 3;
   const uintptr_t buf_lo = (uintptr_t)p.frames, buf_hi = buf_lo + p.frames_bytes;
@@ -110,7 +102,20 @@ __device__ __forceinline__ void issue_step(const Cursor& c, const CropParams& p,
   const uint32_t seg = (uint32_t)c.cw * 3u;
   const int j = lane >> 1, tap = lane & 1;
   int row = -1, b0 = kCoefOne, b1 = 0;
-  if (j < nr) y_entry(c, S, y0 + j, tap, row, b0, b1);
+  if (j < nr) {
+    const int y = y0 + j;
+    if (c.mode == kResizeCopy) {
+      row = tap ? -1 : y;
+    } else if (c.mode == kResizeBox2) {
+      row = 2 * y + tap;
+      b0 = b1 = kCoefOne / 2;
+    } else {
+      const AxisCoef k = axis_coef(y, sc_y, c.ch, false);
+      b0 = k.w0;
+      b1 = k.w1;
+      row = tap ? (k.w1 != 0 ? clampi(k.s0 + 1, 0, c.ch - 1) : -1) : clampi(k.s0, 0, c.ch - 1);
+    }
+  }
   const unsigned same = __match_any_sync(0xffffffffu, row);
   const int leader = __ffs(same) - 1;
   const bool copy = leader == lane && row >= 0;
@@ -120,20 +125,12 @@ __device__ __forceinline__ void issue_step(const Cursor& c, const CropParams& p,
   const int off = slot * c.slot_bytes + (int)(g_lo & 15);
   uintptr_t a_lo = 0, a_hi = 0;
   uint32_t bulk = 0;
+  uint8_t* s = stage + off;  // where crop byte g_lo lands
   if (copy) {
     a_lo = max(g_lo & ~(uintptr_t)15, (buf_lo + 15) & ~(uintptr_t)15);
     a_hi = min((g_lo + seg + 15) & ~(uintptr_t)15, buf_hi & ~(uintptr_t)15);
-    if (a_hi > a_lo) bulk = (uint32_t)(a_hi - a_lo);
-  }
-  uint32_t tx = bulk;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) tx += __shfl_xor_sync(0xffffffffu, tx, o);
-  if (lane == 0) mbar_expect_tx(bar, tx);
-  __syncwarp();
-  if (copy) {
-    uint8_t* s = stage + off;  // where crop byte g_lo lands
-    if (bulk) {
-      bulk_g2s(s + (ptrdiff_t)(a_lo - g_lo), reinterpret_cast<const void*>(a_lo), bulk, bar);
+    if (a_hi > a_lo) {
+      bulk = (uint32_t)(a_hi - a_lo);
       for (uintptr_t q = g_lo; q < a_lo; ++q) s[q - g_lo] = *reinterpret_cast<const uint8_t*>(q);
       for (uintptr_t q = max(a_hi, g_lo); q < g_lo + seg; ++q) s[q - g_lo] = *reinterpret_cast<const uint8_t*>(q);
     } else {
@@ -149,19 +146,36 @@ __device__ __forceinline__ void issue_step(const Cursor& c, const CropParams& p,
       plan[j].off1 = row >= 0 ? off : 0;  // unused tap: any valid offset, its weight is 0
     }
   }
+  uint32_t tx = bulk;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) tx += __shfl_xor_sync(0xffffffffu, tx, o);
+  __syncwarp();  // plan and lane-copied bytes are ordered before the releasing arrive
+  if (lane == 0) mbar_expect_tx(full, tx);
+  __syncwarp();
+  if (bulk) bulk_g2s(s + (ptrdiff_t)(a_lo - g_lo), reinterpret_cast<const void*>(a_lo), bulk, full);
 }
 
-__global__ void __launch_bounds__(kCropThreads) crop_resize_kernel(const CropParams p) {
+// Six bytes starting at byte address `a` of the staging buffer -> (lo = bytes 0..3, hi = 4..7).
+__device__ __forceinline__ void load6(const uint32_t* stage32, int a, uint32_t& lo, uint32_t& hi) {
+  const uint32_t* w = stage32 + (a >> 2);
+  const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+  const uint32_t sh = (uint32_t)(a & 3) << 3;
+  lo = __funnelshift_r(w0, w1, sh);
+  hi = __funnelshift_r(w1, w2, sh);
+}
+
+__global__ void __launch_bounds__(kCropThreads, 3) crop_resize_kernel(const CropParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ float lut[3][256 * kLutRep];
   __shared__ YPlan yplan[2][kBandRows];
-  __shared__ __align__(8) uint64_t bar[2];
+  __shared__ double scx[2];  // OpenCV scale_x of the step's ROI, from the producer
+  __shared__ __align__(8) uint64_t full[2], empty[2];
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
   const int S = p.out_size;
   const int xg = (S + 3) >> 2;
-  int4* xoff4 = reinterpret_cast<int4*>(smem + 2 * (size_t)p.stage_bytes);  // [xg] byte offsets
-  int4* coef4 = xoff4 + xg;                                               // [xg] a0 | a1 << 16
+  int* xoff = reinterpret_cast<int*>(smem + 2 * (size_t)p.stage_bytes);  // [2][4*xg] byte offsets
+  int* coef = xoff + 8 * xg;                                           // [2][4*xg] a0 | a1 << 16
   const int total = p.total_dev ? min(*p.total_dev, p.roi_slots) : p.total_host;
   const int items = total * p.bands;
   const bool vec_ok = (S & 3) == 0;
@@ -173,105 +187,116 @@ __global__ void __launch_bounds__(kCropThreads) crop_resize_kernel(const CropPar
     for (int c = 0; c < 3; ++c) lut[c][i] = __fdiv_rn(__fsub_rn(u, p.mean[c]), p.stdv[c]);  // :270
   }
   if (tid == 0) {
-    mbar_init(&bar[0], 1);
-    mbar_init(&bar[1], 1);
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_init(&empty[0], kCropConsumers / 32);
+    mbar_init(&empty[1], kCropConsumers / 32);
     mbar_fence_init();
   }
   __syncthreads();
 
   Cursor cur;
   bool have = load_item(cur, p, blockIdx.x, items);
-  if (have && !cur.empty && tid < 32) issue_step(cur, p, smem, yplan[0], &bar[0], lane);
-  uint32_t phase0 = 0, phase1 = 0;
 
+  if (tid >= kCropConsumers) {
+    // =============================== producer warp ====================================
+    double sc_y = 0.0;
+    for (int s = 0; have; ++s) {
+      const int buf = s & 1;
+      if (s >= 2) mbar_wait(&empty[buf], ((s >> 1) - 1) & 1);  // consumers released this buffer
+      if (cur.sb == 0 && !cur.empty) {
+        sc_y = axis_scale(S, cur.ch);
+        if (lane == 0) scx[buf] = axis_scale(S, cur.cw);
+      }
+      produce_step(cur, p, sc_y, smem + (size_t)buf * p.stage_bytes, yplan[buf], &full[buf], lane);
+      have = advance(cur, p, items);
+    }
+    return;
+  }
+
+  // ================================= consumer warps ====================================
+  const uint32_t sel[3] = {0x30u, 0x41u, 0x52u};  // PRMT selectors: (byte c of lo, byte c+3 of lo:hi)
+  const int rep = lane & (kLutRep - 1);
+  int n_item = 0;
+  const int dj = kCropConsumers / xg, dg = kCropConsumers - dj * xg;
   for (int s = 0; have; ++s) {
     const int buf = s & 1;
-    Cursor nxt = cur;
-    const bool have_next = advance(nxt, p, items);
-    // prefetch the next step into the other buffer (its readers finished one iteration ago)
-    if (have_next && !nxt.empty && tid < 32)
-      issue_step(nxt, p, smem + (size_t)(buf ^ 1) * p.stage_bytes, yplan[buf ^ 1], &bar[buf ^ 1], lane);
-
-    // x table of this ROI, once per item (previous item's readers are past the last barrier)
-    if (cur.sb == 0 && !cur.empty) {
-      for (int x = tid; x < 4 * xg; x += kCropThreads) {
-        const int xc = min(x, S - 1);
-        int xo, a0, a1;
-        if (cur.mode == kResizeCopy) {
-          xo = xc * 3, a0 = kCoefOne, a1 = 0;
-        } else if (cur.mode == kResizeBox2) {
-          xo = xc * 6, a0 = a1 = kCoefOne / 2;
-        } else {
-          const AxisCoef k = axis_coef(xc, axis_scale(S, cur.cw), cur.cw, true);
-          xo = k.s0 * 3, a0 = k.w0, a1 = k.w1;
+    mbar_wait(&full[buf], (s >> 1) & 1);
+    if (cur.sb == 0) {
+      ++n_item;
+      if (!cur.empty) {
+        // x table of this ROI (double-buffered by item parity), then a consumers-only barrier
+        int* xo_t = xoff + (n_item & 1) * 4 * xg;
+        int* cf_t = coef + (n_item & 1) * 4 * xg;
+        const double sc_x = scx[buf];
+        for (int x = tid; x < 4 * xg; x += kCropConsumers) {
+          const int xc = min(x, S - 1);
+          int xo, a0, a1;
+          if (cur.mode == kResizeCopy) {
+            xo = xc * 3, a0 = kCoefOne, a1 = 0;
+          } else if (cur.mode == kResizeBox2) {
+            xo = xc * 6, a0 = a1 = kCoefOne / 2;
+          } else {
+            const AxisCoef k = axis_coef(xc, sc_x, cur.cw, true);
+            xo = k.s0 * 3, a0 = k.w0, a1 = k.w1;
+          }
+          xo_t[x] = xo;
+          cf_t[x] = a0 | (a1 << 16);
         }
-        reinterpret_cast<int*>(xoff4)[x] = xo;
-        reinterpret_cast<int*>(coef4)[x] = a0 | (a1 << 16);
-      }
-    }
-    __syncthreads();  // x table, row plan and lane-copied bytes of this step are visible
-    if (!cur.empty) {
-      if (buf == 0) {
-        mbar_wait(&bar[0], phase0);
-        phase0 ^= 1;
-      } else {
-        mbar_wait(&bar[1], phase1);
-        phase1 ^= 1;
+        named_barrier_sync(1, kCropConsumers);
       }
     }
 
-    // ---- compute: warp per output row, 4 pixels x 3 channels per lane --------------------
-    const uint8_t* stage = smem + (size_t)buf * p.stage_bytes;
+    const uint32_t* stage32 = reinterpret_cast<const uint32_t*>(smem + (size_t)buf * p.stage_bytes);
+    const int4* xo4 = reinterpret_cast<const int4*>(xoff + (n_item & 1) * 4 * xg);
+    const int4* cf4 = reinterpret_cast<const int4*>(coef + (n_item & 1) * 4 * xg);
     const int y0 = cur.y_band + cur.sb * cur.sub_rows;
     const int nr = min(cur.sub_rows, cur.rows - cur.sb * cur.sub_rows);
-    const int rep = lane & (kLutRep - 1);
-    for (int j = warp; j < nr; j += kCropWarps) {
-      const YPlan yp = yplan[buf][j];
-      const uint8_t* s0 = stage + yp.off0;
-      const uint8_t* s1 = stage + yp.off1;
-      float* orow = p.out + ((size_t)cur.r * 3) * plane + (size_t)(y0 + j) * S;
-      for (int g = lane; g < xg; g += 32) {
-        uint32_t px[4][3];
-        if (cur.empty) {
+    float* obase = p.out + ((size_t)cur.r * 3) * plane + (size_t)y0 * S;
+
+    int j = tid / xg, g = tid - j * xg;
+    for (int it = tid; it < nr * xg; it += kCropConsumers, j += dj, g += dg) {
+      if (g >= xg) g -= xg, ++j;
+      uint32_t px[4][3];
+      if (cur.empty) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) px[k][0] = px[k][1] = px[k][2] = 0;  // mobilenet_preprocess.py:266-267
-        } else {
-          const int4 xo4 = xoff4[g];
-          const int4 cf4 = coef4[g];
-          const int xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w};
-          const int cf[4] = {cf4.x, cf4.y, cf4.z, cf4.w};
+        for (int k = 0; k < 4; ++k) px[k][0] = px[k][1] = px[k][2] = 0;  // mobilenet_preprocess.py:266-267
+      } else {
+        const YPlan yp = yplan[buf][j];
+        const int4 xv = xo4[g];
+        const int4 cv = cf4[g];
+        const int xo[4] = {xv.x, xv.y, xv.z, xv.w};
+        const uint32_t cf[4] = {(uint32_t)cv.x, (uint32_t)cv.y, (uint32_t)cv.z, (uint32_t)cv.w};
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int a0 = cf[k] & 0xffff, a1 = cf[k] >> 16;
-            const uint8_t* a = s0 + xo[k];
-            const uint8_t* b = s1 + xo[k];
+        for (int k = 0; k < 4; ++k) {
+          uint32_t lo0, hi0, lo1, hi1;
+          load6(stage32, yp.off0 + xo[k], lo0, hi0);
+          load6(stage32, yp.off1 + xo[k], lo1, hi1);
 #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-              // branch-free: a zero weight multiplies whatever byte sits there (always inside
-              // the staging buffer) by 0, exactly as if the tap had been skipped
-              const int h0 = a[c] * a0 + a[c + 3] * a1;
-              const int h1 = b[c] * a0 + b[c + 3] * a1;
-              px[k][c] = (uint32_t)vresize(h0, h1, yp.b0, yp.b1);
-            }
-          }
-        }
-        float* o = orow + (g << 2);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          const float* l = lut[c] + rep;
-          if (vec_ok) {
-            st_stream_f4(o + c * plane, l[px[0][c] * kLutRep], l[px[1][c] * kLutRep],
-                         l[px[2][c] * kLutRep], l[px[3][c] * kLutRep]);
-          } else {
-            for (int k = 0; k < 4 && (g << 2) + k < S; ++k)
-              st_stream_f1(o + c * plane + k, l[px[k][c] * kLutRep]);
+          for (int c = 0; c < 3; ++c) {
+            // h = p[c]*a0 + p[c+3]*a1 in one IDP.2A; a zero weight multiplies whatever byte
+            // sits there (always inside the staging buffer) by 0
+            const int h0 = (int)__dp2a_lo(cf[k], __byte_perm(lo0, hi0, sel[c]), 0u);
+            const int h1 = (int)__dp2a_lo(cf[k], __byte_perm(lo1, hi1, sel[c]), 0u);
+            px[k][c] = (uint32_t)vresize(h0, h1, yp.b0, yp.b1);
           }
         }
       }
+      float* o = obase + (size_t)j * S + (g << 2);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float* l = lut[c] + rep;
+        if (vec_ok) {
+          st_stream_f4(o + c * plane, l[px[0][c] * kLutRep], l[px[1][c] * kLutRep],
+                       l[px[2][c] * kLutRep], l[px[3][c] * kLutRep]);
+        } else {
+          for (int k = 0; k < 4 && (g << 2) + k < S; ++k) st_stream_f1(o + c * plane + k, l[px[k][c] * kLutRep]);
+        }
+      }
     }
-    __syncthreads();  // everyone is done with this staging buffer, its plan and the x table
-    cur = nxt;
-    have = have_next;
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[buf]);  // this warp is done with the staging buffer + plan
+    have = advance(cur, p, items);
   }
 }
 
@@ -303,7 +328,7 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   size_t stage = 24 * 1024;
   if (stage < 2 * widest) stage = 2 * widest;
   const size_t xg = ((size_t)out_size + 3) / 4;
-  const size_t smem = 2 * stage + 2 * xg * sizeof(int4);
+  const size_t smem = 2 * stage + 4 * xg * sizeof(int4);
   IA_RETURN_IF(smem > 180 * 1024 || stage >= (1u << 20), IA_ERR_UNSUPPORTED);
   c.stage_bytes = (int)stage;
   int dev = 0, sms = 148, per_sm = 1;
