@@ -323,9 +323,9 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   c.out = out;
   const long long items = (long long)c.bands * roi_slots;
   IA_RETURN_IF(items > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
-  // two staging buffers; each holds at least two full-width rows, normally 24 KB
+  // two staging buffers; each holds at least two full-width rows, normally 21 KB
   const size_t widest = ((size_t)src_w * 3 + 30 + 15) & ~(size_t)15;
-  size_t stage = 24 * 1024;
+  size_t stage = 21 * 1024;  // 16 slots of a ~420-px crop row (8+8 row sub-bands); 3 CTAs per SM
   if (stage < 2 * widest) stage = 2 * widest;
   const size_t xg = ((size_t)out_size + 3) / 4;
   const size_t smem = 2 * stage + 4 * xg * sizeof(int4);
