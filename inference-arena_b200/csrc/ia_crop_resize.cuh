@@ -4,7 +4,7 @@
 // Work is a stream of steps; a step is a sub-band (<= 16 output rows, sized to one staging
 // buffer) of one ROI.  CTAs are persistent (grid = SMs x resident CTAs) and stride over the
 // (ROI, band) items; the ROI total is read from device memory, so nothing returns to the
-// host between NMS and here.  A CTA is 8 consumer warps + 1 producer warp, coupled only by
+// host between NMS and here.  A CTA is 7 consumer warps + 1 producer warp, coupled only by
 // mbarriers (full[2] / empty[2]) — no CTA-wide barrier in the loop:
 //   producer: lane (row j, tap) evaluates OpenCV's yofs/beta entry, duplicates are removed
 //           with __match_any_sync, the row plan is published, and each distinct crop row
@@ -27,7 +27,9 @@
 
 namespace ia {
 
-constexpr int kCropConsumers = 256;
+// 7 consumer warps: 224 lanes = 4 output rows x 56 four-pixel groups at out_size 224, so an
+// 8-row step is exactly two full passes (no idle lanes); + 1 producer warp = 256 threads.
+constexpr int kCropConsumers = 224;
 constexpr int kCropThreads = kCropConsumers + 32;
 constexpr int kBandRows = 16;
 constexpr int kLutRep = 8;  // copies of each LUT entry, one per (lane & 7): fewer bank conflicts
