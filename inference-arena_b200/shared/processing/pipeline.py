@@ -74,9 +74,38 @@ class DevicePipeline:
         return PipelineOutput(tensor, dets, keep, count, status, crops, offsets, rois)
 
 
+class HostTicket:
+    """Handle of one submitted batch: ``wait()`` blocks until its outputs are in host memory
+    and returns them (views into the pipeline's pinned result set; valid until the
+    pipeline's next-but-one ``submit``)."""
+
+    def __init__(self, owner, slots, pending, views: dict) -> None:
+        self._owner, self._slots, self._pending, self._views, self.done = owner, slots, pending, views, False
+
+    def finish_last_chunk(self) -> None:
+        if self._pending is not None:
+            self._owner._copy_crops(self._pending)
+            self._pending = None
+
+    def wait(self) -> dict:
+        if not self.done:
+            self.finish_last_chunk()
+            for slot in self._slots:
+                ev = torch.cuda.Event()
+                ev.record(self._owner.streams[slot])
+                ev.synchronize()
+            self.done = True
+        return self._views
+
+
 class HostPipeline:
     """Host buffers in, host buffers out (the e2e path).  ``chunk`` images move per stream
-    slot; ``slots`` chunks are in flight at once (copy-in / compute / copy-out overlap)."""
+    slot; ``slots`` chunks are in flight at once, so copy-in, kernels and copy-out overlap.
+    ``submit`` is asynchronous and double-buffers the pinned result buffers: the copies of
+    batch k+1 start while batch k is still draining, which keeps the PCIe link busy in both
+    directions; ``run`` is the synchronous form."""
+
+    RESULT_SETS = 2
 
     def __init__(self, max_batch: int, src_h: int, src_w: int, device: torch.device | str = "cuda",
                  chunk: int = 32, slots: int = 3, **kw) -> None:
@@ -95,55 +124,100 @@ class HostPipeline:
         def pinned(shape, dtype):
             return torch.empty(shape, dtype=dtype, pin_memory=True)
 
-        self.h_tensor = pinned((max_batch, 3, p.target, p.target), torch.float32)
-        self.h_dets = pinned((max_batch, p.max_det, 6), torch.float32)
-        self.h_keep = pinned((max_batch, p.max_det), torch.int32)
-        self.h_count = pinned((max_batch,), torch.int32)
-        self.h_status = pinned((max_batch,), torch.int32)
-        self.h_crops = pinned((max_batch * self.rpi, 3, p.crop_size, p.crop_size), torch.float32)
-        self.h_offsets = pinned((max_batch // chunk + 1, chunk + 1), torch.int32)
+        nchunks = (max_batch + chunk - 1) // chunk
+        self.results = [{
+            "tensor": pinned((max_batch, 3, p.target, p.target), torch.float32),
+            "dets": pinned((max_batch, p.max_det, 6), torch.float32),
+            "keep": pinned((max_batch, p.max_det), torch.int32),
+            "count": pinned((max_batch,), torch.int32),
+            "status": pinned((max_batch,), torch.int32),
+            "crops": pinned((max_batch * self.rpi, 3, p.crop_size, p.crop_size), torch.float32),
+            "roi_offsets": pinned((nchunks, chunk + 1), torch.int32),
+        } for _ in range(self.RESULT_SETS)]
+        self._tickets: list[HostTicket | None] = [None] * self.RESULT_SETS
+        self._submits = 0
+        self._chunks = 0
+        self.last_d2h_bytes = 0
 
     @property
     def h2d_bytes_per_image(self) -> int:
         p = self.pipes[0]
         return self.src_h * self.src_w * 3 + p.anchors * (5 + p.classes) * 4
 
-    def d2h_bytes(self, n: int, total_rois: int) -> int:
-        p = self.pipes[0]
-        per_image = 3 * p.target * p.target * 4 + p.max_det * (6 * 4 + 4) + 8 + 4
-        return n * per_image + total_rois * 3 * p.crop_size * p.crop_size * 4
+    def d2h_bytes(self, n: int) -> int:
+        """Bytes copied back by the most recent batch (counted from the tensors copied: the
+        fixed per-image outputs plus exactly the crops that exist)."""
+        return self.last_d2h_bytes
 
-    def run(self, frames: torch.Tensor, heads: torch.Tensor) -> dict:
+    def _copy_crops(self, pending) -> None:
+        """Second half of a chunk: once its ROI total has reached the host, copy back exactly
+        that many crops (instead of the bounded slab) on the chunk's own stream."""
+        slot, ev, res, ci, lo, m, crops = pending
+        ev.synchronize()
+        total = min(int(res["roi_offsets"][ci, m]), m * self.rpi)
+        if total:
+            with torch.cuda.stream(self.streams[slot]):
+                base = lo * self.rpi
+                res["crops"][base : base + total].copy_(crops[:total], non_blocking=True)
+        self.last_d2h_bytes += total * crops[0].numel() * 4
+
+    def submit(self, frames: torch.Tensor, heads: torch.Tensor) -> HostTicket:
         """``frames`` uint8 [N,H,W,3] and ``heads`` float32 [N,A,85]: pinned (or pageable) HOST
-        tensors.  Returns host views: tensor, dets, keep, count, status, crops (per chunk,
-        ``rpi`` slots per image) and per-chunk roi offsets.  Synchronises before returning."""
+        tensors, which must stay untouched until the ticket has been waited on."""
         n = frames.shape[0]
         assert n <= self.max_batch
+        rs = self._submits % self.RESULT_SETS
+        self._submits += 1
+        if self._tickets[rs] is not None:
+            self._tickets[rs].wait()  # that result set is about to be overwritten
+        for t in self._tickets:  # an earlier batch's last chunk still owns a slot's crop buffer
+            if t is not None:
+                t.finish_last_chunk()
+        res = self.results[rs]
+        p = self.pipes[0]
+        per_image = 3 * p.target * p.target * 4 + p.max_det * (6 * 4 + 4) + 4 + 4
+        self.last_d2h_bytes = n * per_image
         cur = torch.cuda.current_stream(self.device)
         for s in self.streams:
             s.wait_stream(cur)
+        used = set()
+        pending = None
         for ci, lo in enumerate(range(0, n, self.chunk)):
             hi = min(lo + self.chunk, n)
             m = hi - lo
-            slot = ci % self.slots
+            slot = self._chunks % self.slots
+            self._chunks += 1
+            used.add(slot)
             pipe = self.pipes[slot]
             with torch.cuda.stream(self.streams[slot]):
                 df, dh = self.d_frames[slot][:m], self.d_heads[slot][:m]
                 df.copy_(frames[lo:hi], non_blocking=True)
                 dh.copy_(heads[lo:hi], non_blocking=True)
                 out = pipe.run(df, dh)
-                self.h_tensor[lo:hi].copy_(out.tensor, non_blocking=True)
-                self.h_dets[lo:hi].copy_(out.dets, non_blocking=True)
-                self.h_keep[lo:hi].copy_(out.keep, non_blocking=True)
-                self.h_count[lo:hi].copy_(out.count, non_blocking=True)
-                self.h_status[lo:hi].copy_(out.status, non_blocking=True)
-                self.h_offsets[ci, : m + 1].copy_(out.roi_offsets, non_blocking=True)
-                # ROI count is only known on the device: copy the chunk's bounded crop slab
-                rows = m * self.rpi
-                self.h_crops[lo * self.rpi : lo * self.rpi + rows].copy_(out.crops[:rows], non_blocking=True)
-        for s in self.streams:
-            cur.wait_stream(s)
-        cur.synchronize()
-        return {"tensor": self.h_tensor[:n], "dets": self.h_dets[:n], "keep": self.h_keep[:n],
-                "count": self.h_count[:n], "status": self.h_status[:n], "crops": self.h_crops,
-                "roi_offsets": self.h_offsets}
+                res["roi_offsets"][ci, : m + 1].copy_(out.roi_offsets, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                res["tensor"][lo:hi].copy_(out.tensor, non_blocking=True)
+                res["dets"][lo:hi].copy_(out.dets, non_blocking=True)
+                res["keep"][lo:hi].copy_(out.keep, non_blocking=True)
+                res["count"][lo:hi].copy_(out.count, non_blocking=True)
+                res["status"][lo:hi].copy_(out.status, non_blocking=True)
+                self.last_d2h_bytes += (m + 1) * 4
+            if pending is not None:
+                self._copy_crops(pending)  # previous chunk: its total is on the host by now
+            pending = (slot, ev, res, ci, lo, m, out.crops)
+        views = {"tensor": res["tensor"][:n], "dets": res["dets"][:n], "keep": res["keep"][:n],
+                 "count": res["count"][:n], "status": res["status"][:n], "crops": res["crops"],
+                 "roi_offsets": res["roi_offsets"]}
+        ticket = HostTicket(self, sorted(used), pending, views)
+        self._tickets[rs] = ticket
+        return ticket
+
+    def run(self, frames: torch.Tensor, heads: torch.Tensor) -> dict:
+        """Synchronous form: returns when every output of the batch is in host memory."""
+        return self.submit(frames, heads).wait()
+
+    def drain(self) -> None:
+        for t in self._tickets:
+            if t is not None:
+                t.wait()

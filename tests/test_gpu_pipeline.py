@@ -1,0 +1,77 @@
+"""The whole chain through DevicePipeline (device-resident) and HostPipeline (pinned host
+buffers in and out, chunked over streams, asynchronous submits) vs the oracle: the same
+five calls the reference makes per request (monolithic/app/inference.py:161-193)."""
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pipeline as O
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle(frames, heads):
+    return [O.run_image(f, h, 0.25, 0.45) for f, h in zip(frames, heads)]
+
+
+def _check_device(out, want):
+    offs = out.roi_offsets.cpu().numpy()
+    for i, (tensor, dets, keep, _, crops) in enumerate(want):
+        k = int(out.count[i])
+        assert int(out.status[i]) == 0 and k == len(keep)
+        assert out.keep[i, :k].cpu().tolist() == keep
+        assert np.array_equal(out.tensor[i : i + 1].cpu().numpy(), tensor)
+        assert np.array_equal(out.dets[i, :k].cpu().numpy(), dets)
+        assert np.array_equal(out.crops[offs[i] : offs[i + 1]].cpu().numpy(), crops)
+
+
+@pytest.mark.parametrize("h,w", [(480, 640), (1080, 1920)])
+def test_device_pipeline(h, w):
+    from shared.processing.pipeline import DevicePipeline
+
+    n = 5
+    frames, heads = synth.frames(n, h, w, seed=60), synth.head_v5(n, seed=61)
+    pipe = DevicePipeline(n, h, w, "cuda")
+    out = pipe.run(torch.from_numpy(frames).cuda(), torch.from_numpy(heads).cuda())
+    torch.cuda.synchronize()
+    _check_device(out, _oracle(frames, heads))
+
+
+def _check_host(res, want, chunk, rpi):
+    for i, (tensor, dets, keep, _, crops) in enumerate(want):
+        k = int(res["count"][i])
+        assert int(res["status"][i]) == 0 and k == len(keep)
+        assert res["keep"][i, :k].tolist() == keep
+        assert np.array_equal(res["tensor"][i : i + 1].numpy(), tensor)
+        assert np.array_equal(res["dets"][i, :k].numpy(), dets)
+        ci, li = divmod(i, chunk)
+        offs = res["roi_offsets"][ci].numpy()
+        base = ci * chunk * rpi
+        got = res["crops"][base + offs[li] : base + offs[li + 1]].numpy()
+        assert np.array_equal(got, crops)
+
+
+def test_host_pipeline_sync_and_async():
+    from shared.processing.pipeline import HostPipeline
+
+    h, w, n, chunk = 480, 640, 7, 3  # 3 chunks, the last one ragged
+    hp = HostPipeline(n, h, w, "cuda", chunk=chunk, slots=2)
+    batches = []
+    for seed in (70, 72, 74):
+        frames, heads = synth.frames(n, h, w, seed=seed), synth.head_v5(n, seed=seed + 1)
+        batches.append((torch.from_numpy(frames).pin_memory(), torch.from_numpy(heads).pin_memory(),
+                        _oracle(frames, heads)))
+    # synchronous
+    res = hp.run(batches[0][0], batches[0][1])
+    _check_host(res, batches[0][2], chunk, hp.rpi)
+    # asynchronous: two batches in flight, result sets rotate
+    t1 = hp.submit(batches[1][0], batches[1][1])
+    t2 = hp.submit(batches[2][0], batches[2][1])
+    _check_host(t1.wait(), batches[1][2], chunk, hp.rpi)
+    t3 = hp.submit(batches[0][0], batches[0][1])  # re-uses t1's result set (already waited)
+    _check_host(t2.wait(), batches[2][2], chunk, hp.rpi)
+    _check_host(t3.wait(), batches[0][2], chunk, hp.rpi)
+    hp.drain()
+    assert hp.d2h_bytes(n) > 0 and hp.h2d_bytes_per_image == h * w * 3 + 25200 * 85 * 4
