@@ -18,7 +18,7 @@
 //           coefficient pair — OpenCV's 11-bit fixed point, bit-identical to cv2.resize
 //           INTER_LINEAR (copy and the exact-2x box average use the same arithmetic with
 //           tables a0=b0=2048 resp. a0=a1=b0=b1=1024, which reduce to the identity and to
-//           (p00+p01+p10+p11+2)>>2).  Then the ((v/255 - mean)/std) LUT, replicated 8x across
+//           (p00+p01+p10+p11+2)>>2).  Then the ((v/255 - mean)/std) LUT, replicated 4x across
 //           banks, and three 128-bit streaming plane stores.
 // The global side sees only wide, fully used requests; byte gathers hit shared memory.
 #pragma once
@@ -32,7 +32,7 @@ namespace ia {
 constexpr int kCropConsumers = 224;
 constexpr int kCropThreads = kCropConsumers + 32;
 constexpr int kBandRows = 16;
-constexpr int kLutRep = 8;  // copies of each LUT entry, one per (lane & 7): fewer bank conflicts
+constexpr int kLutRep = 4;  // copies of each LUT entry, one per (lane & 3): fewer bank conflicts
 
 struct CropParams {
   const uint8_t* frames;
@@ -166,7 +166,7 @@ __device__ __forceinline__ void load6(const uint32_t* stage32, int a, uint32_t& 
   hi = __funnelshift_r(w1, w2, sh);
 }
 
-__global__ void __launch_bounds__(kCropThreads, 3) crop_resize_kernel(const CropParams p) {
+__global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const CropParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ float lut[3][256 * kLutRep];
   __shared__ YPlan yplan[2][kBandRows];
@@ -325,9 +325,9 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   c.out = out;
   const long long items = (long long)c.bands * roi_slots;
   IA_RETURN_IF(items > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
-  // two staging buffers; each holds at least two full-width rows, normally 21 KB
+  // two staging buffers; each holds at least two full-width rows, normally 19 KB
   const size_t widest = ((size_t)src_w * 3 + 30 + 15) & ~(size_t)15;
-  size_t stage = 21 * 1024;  // 16 slots of a ~420-px crop row (8+8 row sub-bands); 3 CTAs per SM
+  size_t stage = 19 * 1024;  // with the 4x LUT and 64 registers: 4 CTAs (28 consumer warps) per SM
   if (stage < 2 * widest) stage = 2 * widest;
   const size_t xg = ((size_t)out_size + 3) / 4;
   const size_t smem = 2 * stage + 4 * xg * sizeof(int4);
