@@ -142,3 +142,22 @@ def test_full_size_properties(D):
         rows = dets[n, :k]
         order = np.lexsort((-rows[:, 4], rows[:, 5]))
         assert np.array_equal(order, np.arange(k))
+
+
+def test_equal_confidences_are_ordered_larger_index_first(D):
+    """The reference leaves the order of equal scores inside a class to numpy's unstable
+    argsort (postprocess.py:129); oracle and kernels both order them larger-index-first."""
+    head = synth.head_v5(1, seed=28, anchors=900, dup=10)
+    rows = np.flatnonzero(head[0, :, 4] >= 0.5)[:6]
+    head[0, rows, 4] = np.float32(0.75)       # identical objectness ...
+    head[0, rows, 5:] = np.float32(0.0)
+    head[0, rows, 5 + 3] = np.float32(0.8)    # ... and class score -> identical confidence
+    head[0, rows, 0] = np.float32(50) + np.arange(6, dtype=np.float32) * 100  # disjoint boxes: all kept
+    head[0, rows, 1] = np.float32(300)
+    head[0, rows, 2:4] = np.float32(40)
+    dets, keep, count, status = _run(D, head, max_det=900)
+    want_dets, want_keep = O.detect_v5(head[0], 0.25, 0.45)
+    k = int(count[0])
+    assert keep[0, :k].tolist() == want_keep and np.array_equal(dets[0, :k], want_dets)
+    tied = [i for i in want_keep if i in set(rows.tolist())]
+    assert tied == sorted(rows.tolist(), reverse=True)
