@@ -277,6 +277,21 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
     out["C3_decode_nms_256x25200x85"] = {"images_per_s": 256 / ms * 1e3, "ms": ms, "algorithmic_bytes": by,
                                          "achieved_gbs": by / ms / 1e6, "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
     del head
+    # ---- N1: the v8 channel-major head the shipped services feed, 256 x 84 x 8400
+    h8 = torch.rand((256, 84, 8400), device=dev) * 0.3
+    h8[:, 0:2] = torch.rand((256, 2, 8400), device=dev) * 640
+    h8[:, 2:4] = 8 + torch.rand((256, 2, 8400), device=dev) * 192
+    sel = torch.rand((256, 8400), device=dev) < 0.012  # ~100 candidates per image at conf 0.5
+    cls = torch.randint(4, 84, (256, 8400), device=dev)
+    bi, ai = sel.nonzero(as_tuple=True)
+    h8[bi, cls[bi, ai], ai] = 0.55 + 0.4 * torch.rand(bi.numel(), device=dev)
+    ws8 = torch.empty(D.lib().ia_decode_nms_workspace_bytes(256, 8400, 4096), dtype=torch.uint8, device=dev)
+    ms = time_loop(lambda: D.decode_nms_cuda(h8, 0.5, IOU, layout="v8", max_candidates=4096, max_det=128,
+                                             workspace=ws8), steps, warmup, dev)
+    by = 256 * 84 * 8400 * 4
+    out["N1_v8_decode_nms_256x84x8400"] = {"images_per_s": 256 / ms * 1e3, "ms": ms, "algorithmic_bytes": by,
+                                           "achieved_gbs": by / ms / 1e6, "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
+    del h8
     # ---- C4: 512 frames 640x480, ~4 ROIs each -> K4
     frames = torch.randint(0, 256, (512, 480, 640, 3), dtype=torch.uint8, device=dev)
     dets_np, count_np = synth.detections(512, seed=33, kmax=8)
