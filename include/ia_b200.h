@@ -64,6 +64,19 @@ int ia_letterbox_geometry(int src_h, int src_w, int target, ia_letterbox_geom* o
 int ia_yolo_preprocess(const uint8_t* frames_dev, int n, int src_h, int src_w, int target,
                        float divisor, float* out_dev, void* stream);
 
+/* Ragged batches: YOLOPreprocessor.preprocess (yolo_preprocess.py:128-174) for
+ * n frames of DIFFERENT sizes in one call — what a service sees with real COCO frames.
+ *   frames_host  HOST array of n descriptors (device pointer + height + width per frame)
+ *   out_dev      float [n, 3, target, target]; image i comes from frames_host[i]
+ * Frames are grouped by shape on the host; each group is one launch whose frame pointers
+ * travel in the kernel parameters (no device scratch, no copies, no synchronisation). */
+typedef struct ia_frame_desc {
+  const uint8_t* data_dev; /* uint8 [h, w, 3], contiguous */
+  int32_t h, w;
+} ia_frame_desc;
+int ia_yolo_preprocess_ragged(const ia_frame_desc* frames_host, int n, int target, float divisor,
+                              float* out_dev, void* stream);
+
 /* letterbox() itself, transforms.py:118-180: uint8 [n, target, target, 3] HWC with the
  * padding colour `pad_rgb` (LETTERBOX_COLOR, transforms.py:37). */
 int ia_letterbox_u8(const uint8_t* frames_dev, int n, int src_h, int src_w, int target,
@@ -163,6 +176,17 @@ int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int src_h, int sr
                              const float mean[3], const float std[3], float* crops_dev,
                              int roi_capacity, int32_t* roi_offsets_dev, int32_t* rois_dev,
                              void* stream);
+
+/* K4 on a ragged batch: as ia_crop_resize_normalize, but every image has its
+ * own size.  frames_dev is a DEVICE array of n descriptors; the letterbox geometry of each
+ * image (scale, padding for `letterbox_target`) is derived on the device in the reference's
+ * float64 arithmetic (transforms.py:153-157), max_src_w bounds the frame widths (it sizes the
+ * shared-memory staging). */
+int ia_crop_resize_normalize_ragged(const ia_frame_desc* frames_dev, int n, int max_src_w,
+                                    const float* dets_dev, const int32_t* count_dev, int max_det,
+                                    int letterbox_target, int out_size, const float mean[3],
+                                    const float std[3], float* crops_dev, int roi_capacity,
+                                    int32_t* roi_offsets_dev, int32_t* rois_dev, void* stream);
 
 /* The same resize+normalise+CHW on explicit rectangles (no detection input):
  * rois_dev int32 [num_rois, 8] as above.  With one ROI covering a whole image this is

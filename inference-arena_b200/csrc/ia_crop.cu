@@ -32,7 +32,21 @@ struct RoiParams {
   int roi_capacity;
   int* offsets;  // [n+1]
   int* rois;     // [capacity, 8]
+  const ia_frame_desc* descs;  // ragged: per-image size (device); geometry derived per image
+  int target;                  // letterbox target used with descs
 };
+
+// Letterbox geometry of one frame on the device, in the reference's float64 arithmetic
+// (transforms.py:153-157,174-175): same IEEE operations as ia_letterbox_geometry on the host.
+__device__ __forceinline__ void device_geometry(int h, int w, int target, float& scale, int& pad_w, int& pad_h) {
+  const double sh = __ddiv_rn((double)target, (double)h), sw = __ddiv_rn((double)target, (double)w);
+  const double sc = sh < sw ? sh : sw;
+  const int new_w = __double2int_rz(__dmul_rn((double)w, sc));
+  const int new_h = __double2int_rz(__dmul_rn((double)h, sc));
+  pad_w = (target - new_w) / 2;
+  pad_h = (target - new_h) / 2;
+  scale = __double2float_rn(sc);
+}
 
 // transforms.py:216-228 for one coordinate: (v - pad) / float32(scale), clip to [0, hi].
 __device__ __forceinline__ float unletterbox(float v, int pad, float scale, int hi) {
@@ -88,14 +102,20 @@ __global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams 
     const int before = carry + (warp ? warp_sums[warp - 1] : 0) + incl - c;
     if (i < p.n) {
       p.offsets[i] = before;
+      float scale = p.scale;
+      int pad_w = p.pad_w, pad_h = p.pad_h, src_h = p.src_h, src_w = p.src_w;
+      if (p.descs != nullptr) {
+        src_h = p.descs[i].h;
+        src_w = p.descs[i].w;
+        device_geometry(src_h, src_w, p.target, scale, pad_w, pad_h);
+      }
       for (int k = 0; k < c; ++k) {
         const int r = before + k;
         if (r < p.roi_capacity) {
           const float* d = p.dets + ((size_t)i * p.max_det + k) * 6;
-          write_roi(p.rois + (size_t)r * kRoiInts, i, unletterbox(d[0], p.pad_w, p.scale, p.src_w),
-                    unletterbox(d[1], p.pad_h, p.scale, p.src_h),
-                    unletterbox(d[2], p.pad_w, p.scale, p.src_w),
-                    unletterbox(d[3], p.pad_h, p.scale, p.src_h), p.src_h, p.src_w);
+          write_roi(p.rois + (size_t)r * kRoiInts, i, unletterbox(d[0], pad_w, scale, src_w),
+                    unletterbox(d[1], pad_h, scale, src_h), unletterbox(d[2], pad_w, scale, src_w),
+                    unletterbox(d[3], pad_h, scale, src_h), src_h, src_w);
         }
       }
     }
@@ -185,10 +205,46 @@ extern "C" int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int sr
   a.roi_capacity = roi_capacity;
   a.offsets = roi_offsets_dev;
   a.rois = rois_dev;
+  a.descs = nullptr;
+  a.target = 0;
   roi_rects_kernel<<<1, kRoiThreads, 0, stream>>>(a);
   int rc = launch_status();
   if (rc != IA_OK) return rc;
-  return launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
+  return launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, nullptr, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
+                      out_size, mean, std, crops_dev, stream);
+}
+
+extern "C" int ia_crop_resize_normalize_ragged(const ia_frame_desc* frames_dev, int n, int max_src_w,
+                                               const float* dets_dev, const int32_t* count_dev,
+                                               int max_det, int letterbox_target, int out_size,
+                                               const float mean[3], const float std[3], float* crops_dev,
+                                               int roi_capacity, int32_t* roi_offsets_dev,
+                                               int32_t* rois_dev, void* stream_) {
+  using namespace ia;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IA_RETURN_IF(n < 0 || max_src_w < 1 || max_det < 1 || letterbox_target < 1 || out_size < 1 ||
+                   roi_capacity < 0,
+               IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(!roi_offsets_dev || !mean || !std, IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(n > 0 && (!frames_dev || !dets_dev || !count_dev), IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(roi_capacity > 0 && (!crops_dev || !rois_dev), IA_ERR_INVALID_ARGUMENT);
+  RoiParams a;
+  a.dets = dets_dev;
+  a.count = count_dev;
+  a.n = n;
+  a.max_det = max_det;
+  a.scale = 1.f;
+  a.pad_w = a.pad_h = 0;
+  a.src_h = a.src_w = 1;
+  a.roi_capacity = roi_capacity;
+  a.offsets = roi_offsets_dev;
+  a.rois = rois_dev;
+  a.descs = frames_dev;
+  a.target = letterbox_target;
+  roi_rects_kernel<<<1, kRoiThreads, 0, stream>>>(a);
+  int rc = launch_status();
+  if (rc != IA_OK) return rc;
+  return launch_crops(nullptr, 0, 1, max_src_w, frames_dev, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
                       out_size, mean, std, crops_dev, stream);
 }
 
@@ -199,7 +255,7 @@ extern "C" int ia_resize_normalize_rois(const uint8_t* frames_dev, int n, int sr
   IA_RETURN_IF(n < 0 || src_h < 1 || src_w < 1 || num_rois < 0 || out_size < 1, IA_ERR_INVALID_ARGUMENT);
   if (num_rois == 0) return IA_OK;
   IA_RETURN_IF(!frames_dev || !rois_dev || !crops_dev || !mean || !std, IA_ERR_INVALID_ARGUMENT);
-  return ia::launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, rois_dev, nullptr, num_rois, num_rois, out_size,
+  return ia::launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, nullptr, rois_dev, nullptr, num_rois, num_rois, out_size,
                           mean, std, crops_dev, (cudaStream_t)stream);
 }
 

@@ -38,6 +38,7 @@ struct CropParams {
   const uint8_t* frames;
   size_t frames_bytes;  // n * src_h * src_w * 3: staging never reads outside [frames, frames+bytes)
   int src_h, src_w;
+  const ia_frame_desc* descs;  // ragged batches: per-image pointer/height/width (device) or null
   const int* rois;
   const int* total_dev;  // number of valid ROIs (device) or null
   int total_host;        // used when total_dev is null
@@ -59,7 +60,9 @@ struct Cursor {
   int r, y_band, rows;  // ROI index, first output row of the band, rows in the band
   int empty, cw, ch, mode;
   int slot_bytes;
-  const uint8_t* crop;  // first byte of the crop rectangle in the frame
+  const uint8_t* crop;     // first byte of the crop rectangle in the frame
+  uint32_t row_bytes;      // pitch of the frame the ROI lives in
+  uintptr_t buf_lo, buf_hi;  // that frame's allocation: staging never reads outside it
 };
 
 __device__ __forceinline__ bool load_item(Cursor& c, const CropParams& p, int item, int items) {
@@ -75,7 +78,18 @@ __device__ __forceinline__ bool load_item(Cursor& c, const CropParams& p, int it
   c.cw = c.empty ? 1 : roi[3] - roi[1];
   c.ch = c.empty ? 1 : roi[4] - roi[2];
   c.mode = resize_mode(c.ch, c.cw, S, S);
-  c.crop = p.frames + ((size_t)roi[0] * p.src_h + roi[2]) * ((size_t)p.src_w * 3) + (size_t)roi[1] * 3;
+  if (p.descs != nullptr) {
+    const ia_frame_desc d = p.descs[roi[0]];
+    c.row_bytes = (uint32_t)d.w * 3u;
+    c.buf_lo = (uintptr_t)d.data_dev;
+    c.buf_hi = c.buf_lo + (size_t)d.h * c.row_bytes;
+    c.crop = d.data_dev + (size_t)roi[2] * c.row_bytes + (size_t)roi[1] * 3;
+  } else {
+    c.row_bytes = (uint32_t)p.src_w * 3u;
+    c.buf_lo = (uintptr_t)p.frames;
+    c.buf_hi = c.buf_lo + p.frames_bytes;
+    c.crop = p.frames + ((size_t)roi[0] * p.src_h + roi[2]) * c.row_bytes + (size_t)roi[1] * 3;
+  }
   c.slot_bytes = (c.cw * 3 + 30 + 15) & ~15;  // aligned superset of one crop row segment
   const int max_slots = p.stage_bytes / c.slot_bytes;
   const int cap = max(1, min(kBandRows, max_slots >> 1));  // two source rows per output row
@@ -97,8 +111,8 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
     return;
   }
   const int S = p.out_size;
-  const size_t row_bytes = (size_t)p.src_w * 3;
-  const uintptr_t buf_lo = (uintptr_t)p.frames, buf_hi = buf_lo + p.frames_bytes;
+  const size_t row_bytes = c.row_bytes;
+  const uintptr_t buf_lo = c.buf_lo, buf_hi = c.buf_hi;
   const int y0 = c.y_band + c.sb * c.sub_rows;
   const int nr = min(c.sub_rows, c.rows - c.sb * c.sub_rows);
   const uint32_t seg = (uint32_t)c.cw * 3u;
@@ -303,7 +317,7 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
 }
 
 static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, int src_w,
-                        const int* rois, const int* total_dev, int total_host, int roi_slots,
+                        const ia_frame_desc* descs, const int* rois, const int* total_dev, int total_host, int roi_slots,
                         int out_size, const float mean[3], const float stdv[3], float* out,
                         cudaStream_t stream) {
   if (roi_slots == 0) return IA_OK;
@@ -312,6 +326,7 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   c.frames_bytes = frames_bytes;
   c.src_h = src_h;
   c.src_w = src_w;
+  c.descs = descs;
   c.rois = rois;
   c.total_dev = total_dev;
   c.total_host = total_host;

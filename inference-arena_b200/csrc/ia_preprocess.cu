@@ -18,9 +18,11 @@
 // HBM traffic = source rows actually needed + the output, each once.
 #include <math.h>
 
+#include <algorithm>
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <vector>
 
 #include "ia_common.cuh"
 
@@ -99,8 +101,20 @@ __host__ __device__ inline bool row_sources(int mode, int dy, int new_h, int src
   return true;
 }
 
-template <bool kOutU8, int kMode>
-__global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams p) {
+// Ragged batches (frames of different sizes): images of one shape are launched together, and
+// their base pointers / output slots travel in the kernel parameters (no device scratch).
+constexpr int kRaggedMax = 256;
+template <bool kRagged>
+struct PreRagged {};
+template <>
+struct PreRagged<true> {
+  const uint8_t* frame[kRaggedMax];
+  int out_index[kRaggedMax];
+};
+
+template <bool kOutU8, int kMode, bool kRagged>
+__global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams p,
+                                                                const __grid_constant__ PreRagged<kRagged> rg) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ float lut[kOutU8 ? 1 : 256 * kPreLutRep];
   __shared__ RowPlan plan[kPreMaxRows];
@@ -112,7 +126,15 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
   const int y_begin = (blockIdx.x % p.groups) * p.rows_per_cta;
   const int rows = min(p.rows_per_cta, p.target - y_begin);
   const uint32_t row_bytes = (uint32_t)p.src_w * 3u;
-  const uint8_t* frame = p.frames + (size_t)img * p.src_h * row_bytes;
+  const uint8_t* frame;
+  int out_img;
+  if constexpr (kRagged) {
+    frame = rg.frame[img];
+    out_img = rg.out_index[img];
+  } else {
+    frame = p.frames + (size_t)img * p.src_h * row_bytes;
+    out_img = img;
+  }
   int2* xtab = reinterpret_cast<int2*>(smem + (size_t)p.slots_cap * p.slot_bytes);
 
   if (tid == 0) {
@@ -239,7 +261,7 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
       }
     }
     if (kOutU8) {
-      uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + (((size_t)img * T + y) * T + x) * 3;
+      uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + (((size_t)out_img * T + y) * T + x) * 3;
       if (vec_ok) {
         uint32_t* o32 = reinterpret_cast<uint32_t*>(o);
         o32[0] = px[0][0] | px[0][1] << 8 | px[0][2] << 16 | px[1][0] << 24;
@@ -250,7 +272,7 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
           for (int c = 0; c < 3; ++c) o[k * 3 + c] = (uint8_t)px[k][c];
       }
     } else {
-      float* o = reinterpret_cast<float*>(p.out) + (((size_t)img * 3) * T + y) * T + x;
+      float* o = reinterpret_cast<float*>(p.out) + (((size_t)out_img * 3) * T + y) * T + x;
       const size_t plane = (size_t)T * T;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -286,20 +308,12 @@ static int max_distinct_rows(int mode, int rows, const ia_letterbox_geom& g, dou
   return worst;
 }
 
-template <bool kOutU8>
-static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, int target,
-                            float divisor, uint32_t pad_rgb, void* out, cudaStream_t stream) {
-  IA_RETURN_IF(n < 0 || src_h < 1 || src_w < 1 || target < 1, IA_ERR_INVALID_ARGUMENT);
-  if (n == 0) return IA_OK;
-  IA_RETURN_IF(!frames || !out, IA_ERR_INVALID_ARGUMENT);
+// Geometry, mode, rows per CTA and staging size for one frame shape (cached: the table walk
+// costs tens of microseconds on the host).
+static int plan_letterbox(int src_h, int src_w, int target, PreParams& p, int& mode, size_t& smem) {
   ia_letterbox_geom g;
   int rc = ia_letterbox_geometry(src_h, src_w, target, &g);
   if (rc != IA_OK) return rc;
-
-  PreParams p;
-  p.frames = frames;
-  p.out = out;
-  p.n = n;
   p.src_h = src_h;
   p.src_w = src_w;
   p.target = target;
@@ -307,15 +321,12 @@ static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, 
   p.new_w = g.new_w;
   p.pad_h = g.pad_h;
   p.pad_w = g.pad_w;
-  p.divisor = divisor;
   p.sc_x = axis_scale(g.new_w, src_w);
   p.sc_y = axis_scale(g.new_h, src_h);
-  p.pad_rgb = pad_rgb;
   p.slot_bytes = (((src_w * 3 + 15) & ~15) + 32);  // row + misalignment + branch-free over-read
-  int mode = resize_mode(src_h, src_w, g.new_h, g.new_w);
+  mode = resize_mode(src_h, src_w, g.new_h, g.new_w);
   const size_t xtab_bytes = mode == kResizeLinear ? (size_t)g.new_w * sizeof(int2) : 0;
-  // rows per CTA: the largest group whose staging buffer leaves room for >= 6 CTAs per SM.
-  // The table walk costs tens of microseconds on the host, so it is done once per geometry.
+  // rows per CTA: the largest group whose staging buffer leaves room for >= 6 CTAs per SM
   int rows = kPreMaxRows, slots = 0;
   {
     static std::mutex mu;
@@ -342,26 +353,86 @@ static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, 
       mode = std::get<2>(it->second);
     }
   }
-  const size_t smem = (size_t)slots * p.slot_bytes + xtab_bytes;
+  smem = (size_t)slots * p.slot_bytes + xtab_bytes;
   IA_RETURN_IF(smem > 200 * 1024, IA_ERR_UNSUPPORTED);
   IA_RETURN_IF((size_t)slots * src_w * 3 >= (1u << 20), IA_ERR_UNSUPPORTED);  // mbarrier tx range
   p.rows_per_cta = rows;
   p.slots_cap = slots;
   p.groups = (target + rows - 1) / rows;
+  return IA_OK;
+}
+
+template <bool kOutU8, bool kRagged>
+static int launch_planned(PreParams& p, int mode, size_t smem, int n, const PreRagged<kRagged>& rg,
+                          cudaStream_t stream) {
+  p.n = n;
   const long long blocks = (long long)p.groups * n;
   IA_RETURN_IF(blocks > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
-
-  void (*kernel)(PreParams) = nullptr;
+  void (*kernel)(PreParams, PreRagged<kRagged>) = nullptr;
   switch (mode) {
-    case kResizeCopy: kernel = letterbox_kernel<kOutU8, kResizeCopy>; break;
-    case kResizeBox2: kernel = letterbox_kernel<kOutU8, kResizeBox2>; break;
-    case kResizeGather: kernel = letterbox_kernel<kOutU8, kResizeGather>; break;
-    default: kernel = letterbox_kernel<kOutU8, kResizeLinear>; break;
+    case kResizeCopy: kernel = letterbox_kernel<kOutU8, kResizeCopy, kRagged>; break;
+    case kResizeBox2: kernel = letterbox_kernel<kOutU8, kResizeBox2, kRagged>; break;
+    case kResizeGather: kernel = letterbox_kernel<kOutU8, kResizeGather, kRagged>; break;
+    default: kernel = letterbox_kernel<kOutU8, kResizeLinear, kRagged>; break;
   }
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  kernel<<<(unsigned)blocks, kPreThreads, smem, stream>>>(p);
+  kernel<<<(unsigned)blocks, kPreThreads, smem, stream>>>(p, rg);
   return launch_status();
+}
+
+template <bool kOutU8>
+static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, int target,
+                            float divisor, uint32_t pad_rgb, void* out, cudaStream_t stream) {
+  IA_RETURN_IF(n < 0 || src_h < 1 || src_w < 1 || target < 1, IA_ERR_INVALID_ARGUMENT);
+  if (n == 0) return IA_OK;
+  IA_RETURN_IF(!frames || !out, IA_ERR_INVALID_ARGUMENT);
+  PreParams p;
+  int mode;
+  size_t smem;
+  int rc = plan_letterbox(src_h, src_w, target, p, mode, smem);
+  if (rc != IA_OK) return rc;
+  p.frames = frames;
+  p.out = out;
+  p.divisor = divisor;
+  p.pad_rgb = pad_rgb;
+  return launch_planned<kOutU8, false>(p, mode, smem, n, PreRagged<false>{}, stream);
+}
+
+// Frames of different sizes: one launch per (shape, chunk of kRaggedMax images).
+static int launch_letterbox_ragged(const ia_frame_desc* frames, int n, int target, float divisor,
+                                   uint32_t pad_rgb, float* out, cudaStream_t stream) {
+  IA_RETURN_IF(n < 0 || target < 1, IA_ERR_INVALID_ARGUMENT);
+  if (n == 0) return IA_OK;
+  IA_RETURN_IF(!frames || !out, IA_ERR_INVALID_ARGUMENT);
+  std::map<std::pair<int, int>, std::vector<int>> by_shape;
+  for (int i = 0; i < n; ++i) {
+    IA_RETURN_IF(!frames[i].data_dev || frames[i].h < 1 || frames[i].w < 1, IA_ERR_INVALID_ARGUMENT);
+    by_shape[std::make_pair(frames[i].h, frames[i].w)].push_back(i);
+  }
+  for (const auto& kv : by_shape) {
+    PreParams p;
+    int mode;
+    size_t smem;
+    int rc = plan_letterbox(kv.first.first, kv.first.second, target, p, mode, smem);
+    if (rc != IA_OK) return rc;
+    p.frames = nullptr;
+    p.out = out;
+    p.divisor = divisor;
+    p.pad_rgb = pad_rgb;
+    const std::vector<int>& idx = kv.second;
+    for (size_t lo = 0; lo < idx.size(); lo += kRaggedMax) {
+      const int m = (int)std::min(idx.size() - lo, (size_t)kRaggedMax);
+      PreRagged<true> rg;
+      for (int k = 0; k < m; ++k) {
+        rg.frame[k] = frames[idx[lo + k]].data_dev;
+        rg.out_index[k] = idx[lo + k];
+      }
+      rc = launch_planned<false, true>(p, mode, smem, m, rg, stream);
+      if (rc != IA_OK) return rc;
+    }
+  }
+  return IA_OK;
 }
 
 }  // namespace ia
@@ -397,4 +468,10 @@ extern "C" int ia_letterbox_u8(const uint8_t* frames_dev, int n, int src_h, int 
   const uint32_t rgb = (uint32_t)pad_rgb[0] | (uint32_t)pad_rgb[1] << 8 | (uint32_t)pad_rgb[2] << 16;
   return ia::launch_letterbox<true>(frames_dev, n, src_h, src_w, target, 255.0f, rgb, out_dev,
                                     (cudaStream_t)stream);
+}
+
+extern "C" int ia_yolo_preprocess_ragged(const ia_frame_desc* frames_host, int n, int target,
+                                         float divisor, float* out_dev, void* stream) {
+  return ia::launch_letterbox_ragged(frames_host, n, target, divisor, 114u | 114u << 8 | 114u << 16,
+                                     out_dev, (cudaStream_t)stream);
 }

@@ -26,6 +26,12 @@ class LetterboxGeom(ctypes.Structure):
                 ("scale", c_double)]
 
 
+class FrameDesc(ctypes.Structure):
+    """``ia_frame_desc`` (include/ia_b200.h): one frame of a ragged batch."""
+
+    _fields_ = [("data_dev", c_void_p), ("h", c_int32), ("w", c_int32)]
+
+
 F3 = c_float * 3
 U3 = ctypes.c_uint8 * 3
 
@@ -34,6 +40,7 @@ _SIGNATURES = {
     "ia_error_string": (c_char_p, [c_int]),
     "ia_letterbox_geometry": (c_int, [c_int, c_int, c_int, POINTER(LetterboxGeom)]),
     "ia_yolo_preprocess": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),
+    "ia_yolo_preprocess_ragged": (c_int, [c_void_p, c_int, c_int, c_float, c_void_p, c_void_p]),
     "ia_letterbox_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, U3, c_void_p, c_void_p]),
     "ia_decode_nms_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "ia_decode_nms": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_float, c_float, c_int, c_int,
@@ -47,6 +54,8 @@ _SIGNATURES = {
     "ia_crop_resize_normalize": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int,
                                          c_float, c_int, c_int, c_int, F3, F3, c_void_p, c_int,
                                          c_void_p, c_void_p, c_void_p]),
+    "ia_crop_resize_normalize_ragged": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
+                                                c_int, F3, F3, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "ia_resize_normalize_rois": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, F3,
                                          F3, c_void_p, c_void_p]),
     "ia_extract_crop_rects": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

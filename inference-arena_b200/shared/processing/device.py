@@ -12,6 +12,7 @@ with no host round trip:
 
 from __future__ import annotations
 
+import ctypes
 from dataclasses import dataclass
 
 import numpy as np
@@ -249,3 +250,57 @@ def imagenet_normalize_cuda(image: torch.Tensor, mean=(0.485, 0.456, 0.406),
             F3(*[float(np.float32(v)) for v in std]), out.data_ptr(), _stream_ptr(image.device)),
             "ia_imagenet_normalize_u8")
     return out
+
+
+# ------------------------------------------------------------------- ragged batches (N2)
+def _frame_descs(frames: list[torch.Tensor]):
+    """ctypes array of ia_frame_desc for a list of uint8 [H,W,3] CUDA tensors."""
+    if not frames:
+        raise ValueError("empty frame list")
+    keep = [_require_cuda(f, torch.uint8, "frame") for f in frames]
+    for f in keep:
+        if f.ndim != 3 or f.shape[2] != 3:
+            raise ValueError(f"Expected [H, W, 3] frames, got {tuple(f.shape)}")
+    arr = (_native.FrameDesc * len(keep))()
+    for i, f in enumerate(keep):
+        arr[i].data_dev, arr[i].h, arr[i].w = f.data_ptr(), f.shape[0], f.shape[1]
+    return arr, keep
+
+
+def preprocess_ragged_cuda(frames: list[torch.Tensor], target: int = 640, divisor: float = 255.0) -> torch.Tensor:
+    """YOLOPreprocessor.preprocess (reference yolo_preprocess.py:128-174) for frames of
+    different sizes: list of uint8 [H_i,W_i,3] CUDA tensors -> float32 [N,3,target,target]."""
+    descs, keep = _frame_descs(frames)
+    dev = keep[0].device
+    out = torch.empty((len(keep), 3, target, target), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().ia_yolo_preprocess_ragged(ctypes.addressof(descs), len(keep), int(target),
+                                              float(np.float32(divisor)), out.data_ptr(), _stream_ptr(dev)),
+              "ia_yolo_preprocess_ragged")
+    return out
+
+
+def crop_ragged_cuda(frames: list[torch.Tensor], dets: torch.Tensor, count: torch.Tensor, target: int = 640,
+                     out_size: int = 224, mean=(0.485, 0.456, 0.406), std=(0.229, 0.224, 0.225),
+                     roi_capacity: int | None = None):
+    """The fan-out (scale_boxes -> extract_crop -> resize -> normalise -> CHW) over frames of
+    different sizes; every image's letterbox geometry is derived on the device.
+    Returns ``(crops, roi_offsets, rois)`` like ``crop_batch_cuda``."""
+    descs, keep = _frame_descs(frames)
+    dev = keep[0].device
+    dets = _require_cuda(dets, torch.float32, "dets")
+    count = _require_cuda(count, torch.int32, "count")
+    n, max_det = len(keep), dets.shape[1]
+    cap = int(roi_capacity) if roi_capacity is not None else n * max_det
+    # the descriptor table lives on the device for this entry point (ROI -> image -> frame)
+    table = torch.frombuffer(bytearray(bytes(descs)), dtype=torch.uint8).to(dev)
+    out = torch.empty((cap, 3, out_size, out_size), dtype=torch.float32, device=dev)
+    offsets = torch.empty((n + 1,), dtype=torch.int32, device=dev)
+    rois = torch.empty((max(cap, 1), 8), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().ia_crop_resize_normalize_ragged(
+            table.data_ptr(), n, max(f.shape[1] for f in keep), dets.data_ptr(), count.data_ptr(), max_det,
+            int(target), int(out_size), F3(*[float(np.float32(v)) for v in mean]),
+            F3(*[float(np.float32(v)) for v in std]), out.data_ptr(), cap, offsets.data_ptr(), rois.data_ptr(),
+            _stream_ptr(dev)), "ia_crop_resize_normalize_ragged")
+    return out, offsets, rois
