@@ -324,6 +324,10 @@ def run_gpu_arm(args) -> None:
         raise RuntimeError("bench.py needs a CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = None
+    if not args.no_numa_bind:  # pinned staging memory should live on the GPU's own NUMA node
+        from shared.processing.numa import bind_to_gpu_numa
+        numa = bind_to_gpu_numa(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     D.lib()
@@ -444,6 +448,7 @@ def run_gpu_arm(args) -> None:
         "gpu_launches": KERNELS_PER_STEP * args.steps,
         "clocks": clocks,
         "rois_per_step": total_rois,
+        "numa_bind": numa,
     }
     if cpu is not None:
         line["cpu_baseline"] = cpu
@@ -503,6 +508,7 @@ def main() -> None:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not pin the process to the GPU's NUMA node")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
