@@ -72,13 +72,31 @@ __device__ __forceinline__ void write_roi(int* roi, int img, float fx1, float fy
   roi[7] = 0;
 }
 
+// scale_boxes + extract_crop for detection k of image i -> ROI record r.
+__device__ __forceinline__ void emit_roi(const RoiParams& p, int i, int k, int r) {
+  if (r >= p.roi_capacity) return;
+  float scale = p.scale;
+  int pad_w = p.pad_w, pad_h = p.pad_h, src_h = p.src_h, src_w = p.src_w;
+  if (p.descs != nullptr) {
+    src_h = p.descs[i].h;
+    src_w = p.descs[i].w;
+    device_geometry(src_h, src_w, p.target, scale, pad_w, pad_h);
+  }
+  const float* d = p.dets + ((size_t)i * p.max_det + k) * 6;
+  write_roi(p.rois + (size_t)r * kRoiInts, i, unletterbox(d[0], pad_w, scale, src_w),
+            unletterbox(d[1], pad_h, scale, src_h), unletterbox(d[2], pad_w, scale, src_w),
+            unletterbox(d[3], pad_h, scale, src_h), src_h, src_w);
+}
+
 __global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams p) {
   __shared__ int warp_sums[32];
   __shared__ int carry;
+  __shared__ int s_before[kRoiThreads], s_cnt[kRoiThreads];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) carry = 0;
   __syncthreads();
   for (int base = 0; base < p.n; base += kRoiThreads) {
+    // ---- exclusive scan of the clamped counts of up to 1024 images ------------------------
     const int i = base + tid;
     const int c = i < p.n ? min(max(p.count[i], 0), p.max_det) : 0;
     int incl = c;
@@ -100,24 +118,20 @@ __global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams 
     }
     __syncthreads();
     const int before = carry + (warp ? warp_sums[warp - 1] : 0) + incl - c;
-    if (i < p.n) {
-      p.offsets[i] = before;
-      float scale = p.scale;
-      int pad_w = p.pad_w, pad_h = p.pad_h, src_h = p.src_h, src_w = p.src_w;
-      if (p.descs != nullptr) {
-        src_h = p.descs[i].h;
-        src_w = p.descs[i].w;
-        device_geometry(src_h, src_w, p.target, scale, pad_w, pad_h);
-      }
-      for (int k = 0; k < c; ++k) {
-        const int r = before + k;
-        if (r < p.roi_capacity) {
-          const float* d = p.dets + ((size_t)i * p.max_det + k) * 6;
-          write_roi(p.rois + (size_t)r * kRoiInts, i, unletterbox(d[0], pad_w, scale, src_w),
-                    unletterbox(d[1], pad_h, scale, src_h), unletterbox(d[2], pad_w, scale, src_w),
-                    unletterbox(d[3], pad_h, scale, src_h), src_h, src_w);
-        }
-      }
+    s_before[tid] = before;
+    s_cnt[tid] = c;
+    if (i < p.n) p.offsets[i] = before;
+    __syncthreads();
+    // ---- rectangles: (image, detection) pairs spread over all threads, so the detection
+    // loads of different images are in flight together -----------------------------------
+    const int chunk_n = min(kRoiThreads, p.n - base);
+    for (int t = tid; t < chunk_n * 32; t += kRoiThreads) {
+      const int li = t >> 5, k = t & 31;
+      if (k < s_cnt[li]) emit_roi(p, base + li, k, s_before[li] + k);
+    }
+    if (p.max_det > 32) {  // rare: more than 32 detections in an image, a warp per image
+      for (int li = warp; li < chunk_n; li += 32)
+        for (int k = 32 + lane; k < s_cnt[li]; k += 32) emit_roi(p, base + li, k, s_before[li] + k);
     }
     __syncthreads();
     if (tid == 0) carry += warp_sums[31];
