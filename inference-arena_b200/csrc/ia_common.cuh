@@ -155,6 +155,20 @@ __device__ __forceinline__ int vresize(int h0, int h1, int b0, int b1) {
   return (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
 }
 
+// Six bytes starting at byte address `a` of the staging buffer -> (lo = bytes 0..3, hi = 4..7).
+__device__ __forceinline__ void load6(const uint32_t* stage32, int a, uint32_t& lo, uint32_t& hi) {
+  const uint32_t* w = stage32 + (a >> 2);
+  const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+  const uint32_t sh = (uint32_t)(a & 3) << 3;
+  lo = __funnelshift_r(w0, w1, sh);
+  hi = __funnelshift_r(w1, w2, sh);
+}
+
+// PRMT selectors pairing (byte c, byte c+3) of the 8 bytes lo:hi — the two taps of channel c.
+__device__ __forceinline__ uint32_t tap_pair(uint32_t lo, uint32_t hi, int c) {
+  return __byte_perm(lo, hi, c == 0 ? 0x30u : (c == 1 ? 0x41u : 0x52u));
+}
+
 // numpy.maximum / numpy.minimum propagate NaN; fmaxf/fminf do not.
 __device__ __forceinline__ float np_max(float a, float b) { return (a != a) ? a : ((b != b) ? b : fmaxf(a, b)); }
 __device__ __forceinline__ float np_min(float a, float b) { return (a != a) ? a : ((b != b) ? b : fminf(a, b)); }

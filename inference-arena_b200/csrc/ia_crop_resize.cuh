@@ -171,15 +171,6 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
   if (bulk) bulk_g2s(s + (ptrdiff_t)(a_lo - g_lo), reinterpret_cast<const void*>(a_lo), bulk, full);
 }
 
-// Six bytes starting at byte address `a` of the staging buffer -> (lo = bytes 0..3, hi = 4..7).
-__device__ __forceinline__ void load6(const uint32_t* stage32, int a, uint32_t& lo, uint32_t& hi) {
-  const uint32_t* w = stage32 + (a >> 2);
-  const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-  const uint32_t sh = (uint32_t)(a & 3) << 3;
-  lo = __funnelshift_r(w0, w1, sh);
-  hi = __funnelshift_r(w1, w2, sh);
-}
-
 __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const CropParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ float lut[3][256 * kLutRep];

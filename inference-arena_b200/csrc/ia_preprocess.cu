@@ -246,16 +246,18 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
         px[k][1] = s[1];
         px[k][2] = s[2];
       } else {
+        // six bytes per row through three aligned word loads + a funnel shift, PRMT pairs the
+        // two taps of a channel, one IDP.2A does p0*w0 + p1*w1 (branch-free: a zero weight
+        // multiplies a byte that is always inside the staging buffer — every slot has 32
+        // spare bytes — by 0)
         const int2 e = xtab[dx];
-        const int w0 = e.y & 0xffff, w1 = e.y >> 16;
-        const uint8_t* a = p0 + e.x;
-        const uint8_t* b = p1 + e.x;
+        uint32_t lo0, hi0, lo1, hi1;
+        load6(reinterpret_cast<const uint32_t*>(smem), rp.off0 + e.x, lo0, hi0);
+        load6(reinterpret_cast<const uint32_t*>(smem), rp.off1 + e.x, lo1, hi1);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          // branch-free: a zero weight multiplies a byte that is always inside the staging
-          // buffer (every slot has 16 spare bytes) by 0
-          const int h0 = a[c] * w0 + a[c + 3] * w1;
-          const int h1 = b[c] * w0 + b[c + 3] * w1;
+          const int h0 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo0, hi0, c), 0u);
+          const int h1 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo1, hi1, c), 0u);
           px[k][c] = (uint32_t)vresize(h0, h1, rp.b0, rp.b1);
         }
       }
