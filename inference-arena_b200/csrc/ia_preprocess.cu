@@ -116,7 +116,7 @@ template <bool kOutU8, int kMode, bool kRagged>
 __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams p,
                                                                 const __grid_constant__ PreRagged<kRagged> rg) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ float lut[kOutU8 ? 1 : 256 * kPreLutRep];
+  __shared__ __align__(16) float lut[kOutU8 ? 4 : 256 * kPreLutRep];
   __shared__ RowPlan plan[kPreMaxRows];
   __shared__ int seg_row[2 * kPreMaxRows];  // source row per (output row, tap), -1 = none
   __shared__ __align__(8) uint64_t bar;
@@ -192,9 +192,12 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
   }
 
   // ---- tables ---------------------------------------------------------------------
-  if (!kOutU8) {
-    for (int i = tid; i < 256 * kPreLutRep; i += kPreThreads)
-      lut[i] = __fdiv_rn((float)(i / kPreLutRep), p.divisor);
+  if (!kOutU8) {  // one exact division per pixel value, then replicate it across the banks
+    static_assert(kPreThreads == 256 && kPreLutRep == 8, "one LUT value per thread, two float4 stores");
+    const float q = __fdiv_rn((float)tid, p.divisor);
+    float4* dst = reinterpret_cast<float4*>(lut + tid * kPreLutRep);
+    dst[0] = make_float4(q, q, q, q);
+    dst[1] = make_float4(q, q, q, q);
   }
   if (kMode == kResizeLinear || kMode == kResizeGather) {
     for (int dx = tid; dx < p.new_w; dx += kPreThreads) {
@@ -236,10 +239,13 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
         px[k][1] = s[1];
         px[k][2] = s[2];
       } else if (kMode == kResizeBox2) {
-        const uint8_t* a = p0 + dx * 6;
-        const uint8_t* b = p1 + dx * 6;
+        uint32_t lo0, hi0, lo1, hi1;  // two adjacent pixels of each of the two rows
+        load6(reinterpret_cast<const uint32_t*>(smem), rp.off0 + dx * 6, lo0, hi0);
+        load6(reinterpret_cast<const uint32_t*>(smem), rp.off1 + dx * 6, lo1, hi1);
 #pragma unroll
-        for (int c = 0; c < 3; ++c) px[k][c] = ((uint32_t)a[c] + a[c + 3] + b[c] + b[c + 3] + 2u) >> 2;
+        for (int c = 0; c < 3; ++c)  // IDP.2A with weights (1, 1): p[c] + p[c+3]
+          px[k][c] = (__dp2a_lo(0x00010001u, tap_pair(lo0, hi0, c), 2u) +
+                      __dp2a_lo(0x00010001u, tap_pair(lo1, hi1, c), 0u)) >> 2;
       } else if (kMode == kResizeGather) {
         const uint8_t* s = p0 + xtab[dx].x;
         px[k][0] = s[0];
