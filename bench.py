@@ -292,6 +292,20 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
     out["N1_v8_decode_nms_256x84x8400"] = {"images_per_s": 256 / ms * 1e3, "ms": ms, "algorithmic_bytes": by,
                                            "achieved_gbs": by / ms / 1e6, "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
     del h8
+    # ---- C1-sized request (one 640x480 frame + one head) through the whole chain: launch-bound,
+    # so the six launches are also replayed from a CUDA graph
+    from shared.processing.pipeline import DevicePipeline, GraphedPipeline
+    f1 = torch.randint(0, 256, (1, 480, 640, 3), dtype=torch.uint8, device=dev)
+    _, h1 = synth_inputs_device(1, dev, seed=1)
+    p1 = DevicePipeline(1, 480, 640, dev)
+    eager_ms = time_loop(lambda: p1.run(f1, h1), max(steps, 50), warmup, dev)
+    g1 = GraphedPipeline(p1, 1)
+    g1.frames.copy_(f1)
+    g1.head.copy_(h1)
+    graph_ms = time_loop(g1.replay, max(steps, 50), warmup, dev)
+    out["C1_single_request_640x480"] = {"eager_us": eager_ms * 1e3, "cuda_graph_us": graph_ms * 1e3,
+                                        "requests_per_s_graph": 1e3 / graph_ms}
+    del g1, p1
     # ---- C4: 512 frames 640x480, ~4 ROIs each -> K4
     frames = torch.randint(0, 256, (512, 480, 640, 3), dtype=torch.uint8, device=dev)
     dets_np, count_np = synth.detections(512, seed=33, kmax=8)

@@ -75,3 +75,16 @@ def test_host_pipeline_sync_and_async():
     _check_host(t3.wait(), batches[0][2], chunk, hp.rpi)
     hp.drain()
     assert hp.d2h_bytes(n) > 0 and hp.h2d_bytes_per_image == h * w * 3 + 25200 * 85 * 4
+
+
+def test_graphed_pipeline_matches_eager():
+    """The chain captured in a CUDA graph replays to the same bits, for changing inputs."""
+    from shared.processing.pipeline import DevicePipeline, GraphedPipeline
+
+    n, h, w = 2, 480, 640
+    gp = GraphedPipeline(DevicePipeline(n, h, w, "cuda"), n)
+    for seed in (90, 92):
+        frames, heads = synth.frames(n, h, w, seed=seed), synth.head_v5(n, seed=seed + 1)
+        out = gp.run(torch.from_numpy(frames).cuda(), torch.from_numpy(heads).cuda())
+        torch.cuda.synchronize()
+        _check_device(out, _oracle(frames, heads))
