@@ -31,7 +31,7 @@ namespace ia {
 // 8-row step is exactly two full passes (no idle lanes); + 1 producer warp = 256 threads.
 constexpr int kCropConsumers = 224;
 constexpr int kCropThreads = kCropConsumers + 32;
-constexpr int kBandRows = 16;
+constexpr int kBandRows = 14;  // two 7-row steps per band: one output row per consumer warp
 constexpr int kLutRep = 4;  // copies of each LUT entry, one per (lane & 3): fewer bank conflicts
 
 struct CropParams {
@@ -181,11 +181,9 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
   const int tid = threadIdx.x, lane = tid & 31;
   const int S = p.out_size;
   const int xg = (S + 3) >> 2;
-  int* xoff = reinterpret_cast<int*>(smem + 2 * (size_t)p.stage_bytes);  // [2][4*xg] byte offsets
-  int* coef = xoff + 8 * xg;                                           // [2][4*xg] a0 | a1 << 16
+  int* xoff = reinterpret_cast<int*>(smem + 2 * (size_t)p.stage_bytes);  // [2][4*xg] int2 (offset, coefs)
   const int total = p.total_dev ? min(*p.total_dev, p.roi_slots) : p.total_host;
   const int items = total * p.bands;
-  const bool vec_ok = (S & 3) == 0;
   const size_t plane = (size_t)S * S;
 
   for (int i = tid; i < 256 * kLutRep; i += kCropThreads) {
@@ -222,10 +220,8 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
   }
 
   // ================================= consumer warps ====================================
-  const uint32_t sel[3] = {0x30u, 0x41u, 0x52u};  // PRMT selectors: (byte c of lo, byte c+3 of lo:hi)
   const int rep = lane & (kLutRep - 1);
   int n_item = 0;
-  const int dj = kCropConsumers / xg, dg = kCropConsumers - dj * xg;
   for (int s = 0; have; ++s) {
     const int buf = s & 1;
     mbar_wait(&full[buf], (s >> 1) & 1);
@@ -233,71 +229,56 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
       ++n_item;
       if (!cur.empty) {
         // x table of this ROI (double-buffered by item parity), then a consumers-only barrier
-        int* xo_t = xoff + (n_item & 1) * 4 * xg;
-        int* cf_t = coef + (n_item & 1) * 4 * xg;
+        int2* xt_w = reinterpret_cast<int2*>(xoff + (n_item & 1) * 8 * xg);
         const double sc_x = scx[buf];
-        for (int x = tid; x < 4 * xg; x += kCropConsumers) {
-          const int xc = min(x, S - 1);
+        for (int x = tid; x < S; x += kCropConsumers) {
           int xo, a0, a1;
           if (cur.mode == kResizeCopy) {
-            xo = xc * 3, a0 = kCoefOne, a1 = 0;
+            xo = x * 3, a0 = kCoefOne, a1 = 0;
           } else if (cur.mode == kResizeBox2) {
-            xo = xc * 6, a0 = a1 = kCoefOne / 2;
+            xo = x * 6, a0 = a1 = kCoefOne / 2;
           } else {
-            const AxisCoef k = axis_coef(xc, sc_x, cur.cw, true);
+            const AxisCoef k = axis_coef(x, sc_x, cur.cw, true);
             xo = k.s0 * 3, a0 = k.w0, a1 = k.w1;
           }
-          xo_t[x] = xo;
-          cf_t[x] = a0 | (a1 << 16);
+          xt_w[x] = make_int2(xo, a0 | (a1 << 16));
         }
         named_barrier_sync(1, kCropConsumers);
       }
     }
 
     const uint32_t* stage32 = reinterpret_cast<const uint32_t*>(smem + (size_t)buf * p.stage_bytes);
-    const int4* xo4 = reinterpret_cast<const int4*>(xoff + (n_item & 1) * 4 * xg);
-    const int4* cf4 = reinterpret_cast<const int4*>(coef + (n_item & 1) * 4 * xg);
+    const int2* xt = reinterpret_cast<const int2*>(xoff + (n_item & 1) * 8 * xg);  // (byte offset, a0 | a1 << 16)
     const int y0 = cur.y_band + cur.sb * cur.sub_rows;
     const int nr = min(cur.sub_rows, cur.rows - cur.sb * cur.sub_rows);
-    float* obase = p.out + ((size_t)cur.r * 3) * plane + (size_t)y0 * S;
+    const int warp = tid >> 5;
 
-    int j = tid / xg, g = tid - j * xg;
-    for (int it = tid; it < nr * xg; it += kCropConsumers, j += dj, g += dg) {
-      if (g >= xg) g -= xg, ++j;
-      uint32_t px[4][3];
+    // one output row per warp, lanes over consecutive pixels: neighbouring lanes read
+    // neighbouring (often the same) staging words and write one 128-byte line per plane
+    for (int j = warp; j < nr; j += kCropConsumers / 32) {
+      float* orow = p.out + ((size_t)cur.r * 3) * plane + (size_t)(y0 + j) * S;
       if (cur.empty) {
+        for (int x = lane; x < S; x += 32) {  // mobilenet_preprocess.py:266-267: a 1x1 black crop
 #pragma unroll
-        for (int k = 0; k < 4; ++k) px[k][0] = px[k][1] = px[k][2] = 0;  // mobilenet_preprocess.py:266-267
-      } else {
-        const YPlan yp = yplan[buf][j];
-        const int4 xv = xo4[g];
-        const int4 cv = cf4[g];
-        const int xo[4] = {xv.x, xv.y, xv.z, xv.w};
-        const uint32_t cf[4] = {(uint32_t)cv.x, (uint32_t)cv.y, (uint32_t)cv.z, (uint32_t)cv.w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          uint32_t lo0, hi0, lo1, hi1;
-          load6(stage32, yp.off0 + xo[k], lo0, hi0);
-          load6(stage32, yp.off1 + xo[k], lo1, hi1);
-#pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            // h = p[c]*a0 + p[c+3]*a1 in one IDP.2A; a zero weight multiplies whatever byte
-            // sits there (always inside the staging buffer) by 0
-            const int h0 = (int)__dp2a_lo(cf[k], __byte_perm(lo0, hi0, sel[c]), 0u);
-            const int h1 = (int)__dp2a_lo(cf[k], __byte_perm(lo1, hi1, sel[c]), 0u);
-            px[k][c] = (uint32_t)vresize(h0, h1, yp.b0, yp.b1);
-          }
+          for (int c = 0; c < 3; ++c) st_stream_f1(orow + c * plane + x, lut[c][rep]);
         }
+        continue;
       }
-      float* o = obase + (size_t)j * S + (g << 2);
+      const YPlan yp = yplan[buf][j];
+#pragma unroll 4
+      for (int x = lane; x < S; x += 32) {
+        const int2 e = xt[x];
+        uint32_t lo0, hi0, lo1, hi1;
+        load6(stage32, yp.off0 + e.x, lo0, hi0);
+        load6(stage32, yp.off1 + e.x, lo1, hi1);
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const float* l = lut[c] + rep;
-        if (vec_ok) {
-          st_stream_f4(o + c * plane, l[px[0][c] * kLutRep], l[px[1][c] * kLutRep],
-                       l[px[2][c] * kLutRep], l[px[3][c] * kLutRep]);
-        } else {
-          for (int k = 0; k < 4 && (g << 2) + k < S; ++k) st_stream_f1(o + c * plane + k, l[px[k][c] * kLutRep]);
+        for (int c = 0; c < 3; ++c) {
+          // h = p[c]*a0 + p[c+3]*a1 in one IDP.2A; a zero weight multiplies whatever byte sits
+          // there (always inside the staging buffer) by 0
+          const int h0 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo0, hi0, c), 0u);
+          const int h1 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo1, hi1, c), 0u);
+          const int v = vresize(h0, h1, yp.b0, yp.b1);
+          st_stream_f1(orow + c * plane + x, lut[c][v * kLutRep + rep]);
         }
       }
     }
