@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
         continue;
       }
       const YPlan yp = yplan[buf][j];
-#pragma unroll 4
+#pragma unroll 7
       for (int x = lane; x < S; x += 32) {
         const int2 e = xt[x];
         uint32_t lo0, hi0, lo1, hi1;
