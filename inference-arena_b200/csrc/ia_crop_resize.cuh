@@ -104,9 +104,14 @@ __device__ __forceinline__ bool advance(Cursor& c, const CropParams& p, int item
 }
 
 // Producer warp: plan + stage the crop rows of step `c`; arrives on `full`.
+// Everything that does not touch shared memory (coefficients, duplicate removal, copy
+// geometry) is computed BEFORE waiting for the consumers to release the buffer.
 __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& p, double sc_y,
-                                             uint8_t* stage, YPlan* plan, uint64_t* full, int lane) {
+                                             uint8_t* stage, YPlan* plan, uint64_t* full,
+                                             uint64_t* empty, int empty_parity, double* scx_slot,
+                                             double sc_x, bool new_roi, int lane) {
   if (c.empty) {  // nothing to stage; keep the barrier protocol uniform
+    if (empty_parity >= 0) mbar_wait(empty, (uint32_t)empty_parity);
     if (lane == 0) mbar_expect_tx(full, 0);
     return;
   }
@@ -145,8 +150,16 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
   if (copy) {
     a_lo = max(g_lo & ~(uintptr_t)15, (buf_lo + 15) & ~(uintptr_t)15);
     a_hi = min((g_lo + seg + 15) & ~(uintptr_t)15, buf_hi & ~(uintptr_t)15);
-    if (a_hi > a_lo) {
-      bulk = (uint32_t)(a_hi - a_lo);
+    if (a_hi > a_lo) bulk = (uint32_t)(a_hi - a_lo);
+  }
+  uint32_t tx = bulk;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) tx += __shfl_xor_sync(0xffffffffu, tx, o);
+
+  if (empty_parity >= 0) mbar_wait(empty, (uint32_t)empty_parity);  // consumers released the buffer
+  if (new_roi && lane == 0) *scx_slot = sc_x;  // OpenCV scale_x for the consumers' x table
+  if (copy) {
+    if (bulk) {
       for (uintptr_t q = g_lo; q < a_lo; ++q) s[q - g_lo] = *reinterpret_cast<const uint8_t*>(q);
       for (uintptr_t q = max(a_hi, g_lo); q < g_lo + seg; ++q) s[q - g_lo] = *reinterpret_cast<const uint8_t*>(q);
     } else {
@@ -162,9 +175,6 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
       plan[j].off1 = row >= 0 ? off : 0;  // unused tap: any valid offset, its weight is 0
     }
   }
-  uint32_t tx = bulk;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) tx += __shfl_xor_sync(0xffffffffu, tx, o);
   __syncwarp();  // plan and lane-copied bytes are ordered before the releasing arrive
   if (lane == 0) mbar_expect_tx(full, tx);
   __syncwarp();
@@ -208,12 +218,15 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
     double sc_y = 0.0;
     for (int s = 0; have; ++s) {
       const int buf = s & 1;
-      if (s >= 2) mbar_wait(&empty[buf], ((s >> 1) - 1) & 1);  // consumers released this buffer
-      if (cur.sb == 0 && !cur.empty) {
+      const int empty_parity = s >= 2 ? (((s >> 1) - 1) & 1) : -1;
+      double sc_x = 0.0;
+      const bool new_roi = cur.sb == 0 && !cur.empty;
+      if (new_roi) {
         sc_y = axis_scale(S, cur.ch);
-        if (lane == 0) scx[buf] = axis_scale(S, cur.cw);
+        sc_x = axis_scale(S, cur.cw);
       }
-      produce_step(cur, p, sc_y, smem + (size_t)buf * p.stage_bytes, yplan[buf], &full[buf], lane);
+      produce_step(cur, p, sc_y, smem + (size_t)buf * p.stage_bytes, yplan[buf], &full[buf], &empty[buf],
+                   empty_parity, &scx[buf], sc_x, new_roi, lane);
       have = advance(cur, p, items);
     }
     return;
