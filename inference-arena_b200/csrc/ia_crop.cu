@@ -24,15 +24,15 @@ constexpr int kRoiInts = 8;
 
 // ------------------------------------------------------------------------------ stage A
 struct RoiParams {
-  const float* dets;
-  const int* count;
+  const float* __restrict__ dets;
+  const int* __restrict__ count;
   int n, max_det;
   float scale;
   int pad_w, pad_h, src_h, src_w;
   int roi_capacity;
-  int* offsets;  // [n+1]
-  int* rois;     // [capacity, 8]
-  const ia_frame_desc* descs;  // ragged: per-image size (device); geometry derived per image
+  int* __restrict__ offsets;  // [n+1]
+  int* __restrict__ rois;     // [capacity, 8]
+  const ia_frame_desc* __restrict__ descs;  // ragged: per-image size (device); geometry derived per image
   int target;                  // letterbox target used with descs
 };
 
@@ -62,14 +62,9 @@ __device__ __forceinline__ void write_roi(int* roi, int img, float fx1, float fy
   int x2 = min(src_w, __float2int_rz(fx2));
   int y2 = min(src_h, __float2int_rz(fy2));
   const int empty = (x2 <= x1 || y2 <= y1) ? 1 : 0;
-  roi[0] = img;
-  roi[1] = x1;
-  roi[2] = y1;
-  roi[3] = x2;
-  roi[4] = y2;
-  roi[5] = empty;
-  roi[6] = 0;
-  roi[7] = 0;
+  int4* out = reinterpret_cast<int4*>(roi);  // records are 32-byte aligned
+  out[0] = make_int4(img, x1, y1, x2);
+  out[1] = make_int4(y2, empty, 0, 0);
 }
 
 // scale_boxes + extract_crop for detection k of image i -> ROI record r.
@@ -91,7 +86,7 @@ __device__ __forceinline__ void emit_roi(const RoiParams& p, int i, int k, int r
 __global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams p) {
   __shared__ int warp_sums[32];
   __shared__ int carry;
-  __shared__ int s_before[kRoiThreads], s_cnt[kRoiThreads];
+  __shared__ int s_before[kRoiThreads];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) carry = 0;
   __syncthreads();
@@ -119,19 +114,20 @@ __global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams 
     __syncthreads();
     const int before = carry + (warp ? warp_sums[warp - 1] : 0) + incl - c;
     s_before[tid] = before;
-    s_cnt[tid] = c;
     if (i < p.n) p.offsets[i] = before;
     __syncthreads();
-    // ---- rectangles: (image, detection) pairs spread over all threads, so the detection
-    // loads of different images are in flight together -----------------------------------
+    // ---- rectangles: one thread per ROI of the chunk (the image is found by a binary search
+    // in the scanned offsets), so only real work is executed and all loads are independent
     const int chunk_n = min(kRoiThreads, p.n - base);
-    for (int t = tid; t < chunk_n * 32; t += kRoiThreads) {
-      const int li = t >> 5, k = t & 31;
-      if (k < s_cnt[li]) emit_roi(p, base + li, k, s_before[li] + k);
-    }
-    if (p.max_det > 32) {  // rare: more than 32 detections in an image, a warp per image
-      for (int li = warp; li < chunk_n; li += 32)
-        for (int k = 32 + lane; k < s_cnt[li]; k += 32) emit_roi(p, base + li, k, s_before[li] + k);
+    const int chunk_total = warp_sums[31];
+    for (int r = tid; r < chunk_total; r += kRoiThreads) {
+      const int target = carry + r;  // global ROI index
+      int lo = 0, hi = chunk_n - 1;  // last image whose first ROI index is <= target and that has ROIs
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (s_before[mid] <= target) lo = mid; else hi = mid - 1;
+      }
+      emit_roi(p, base + lo, target - s_before[lo], target);
     }
     __syncthreads();
     if (tid == 0) carry += warp_sums[31];
