@@ -128,3 +128,30 @@ def test_full_size_c4(D):
         want = _oracle_crops(frames[n_i : n_i + 1], dets[n_i : n_i + 1], count[n_i : n_i + 1], geom)
         got = crops[offsets[n_i] : offsets[n_i + 1]].cpu().numpy()
         assert np.array_equal(got, want)
+
+
+def test_unaligned_frame_buffer_corners(D):
+    """Frames that neither start nor end on a 16-byte boundary, with ROIs in the first and the
+    last bytes of the buffer: the staging copies must clamp their aligned supersets to the
+    buffer and fetch the cut-off bytes one by one."""
+    n, h, w = 2, 37, 333
+    raw = synth.frames(1, 1, n * h * w + 64, seed=8).reshape(-1)
+    buf = _dev(raw)
+    for off in (1, 7, 16, 29):
+        frames_np = raw[off : off + n * h * w * 3].reshape(n, h, w, 3)
+        frames = buf[off : off + n * h * w * 3].view(n, h, w, 3)
+        g = D.letterbox_geometry(h, w, 640)
+        s = np.float32(g.scale)
+
+        def box(x1, y1, x2, y2):  # original-frame rectangle -> letterbox-space detection row
+            return [x1 * s + g.pad_w, y1 * s + g.pad_h, x2 * s + g.pad_w, y2 * s + g.pad_h, 0.9, 0]
+
+        dets = np.zeros((n, 4, 6), np.float32)
+        dets[0, 0] = box(0, 0, 40, 20)        # first bytes of the buffer
+        dets[0, 1] = box(0, 0, w, h)          # whole first frame
+        dets[1, 0] = box(w - 50, h - 9, w, h)  # last bytes of the buffer
+        dets[1, 1] = box(w - 3, h - 2, w, h)
+        count = np.array([2, 2], np.int32)
+        crops, offsets, _ = D.crop_batch_cuda(frames, _dev(dets), _dev(count), g)
+        want = _oracle_crops(frames_np, dets, count, g)
+        assert np.array_equal(crops[:4].cpu().numpy(), want), off
