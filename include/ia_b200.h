@@ -150,6 +150,10 @@ int ia_nms(const float* boxes_dev, const float* scores_dev, const int32_t* class
 int ia_scale_boxes(const float* boxes_dev, int m, int cols, float scale, int pad_w, int pad_h,
                    int orig_h, int orig_w, float* out_dev, void* stream);
 
+/* The same for float64 boxes (numpy keeps the array's precision: all arithmetic in binary64). */
+int ia_scale_boxes_f64(const double* boxes_dev, int m, int cols, double scale, int pad_w, int pad_h,
+                       int orig_h, int orig_w, double* out_dev, void* stream);
+
 /* ---------------------------------------------------------------------------------
  * K4 — fan-out: for every kept detection, scale_boxes -> extract_crop -> bilinear resize
  * to out_size x out_size -> ImageNet normalise -> CHW, reading the NMS output on the
@@ -206,6 +210,25 @@ int ia_extract_crop_rects(const float* boxes_dev, int m, int cols, int image_ind
 /* imagenet_normalize() on uint8 HWC, transforms.py:238-272 -> float HWC (same layout). */
 int ia_imagenet_normalize_u8(const uint8_t* image_dev, size_t pixels, const float mean[3],
                              const float std[3], float* out_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------
+ * float32-input branch.  MobileNetPreprocessor.preprocess on a float32 crop,
+ * src/shared/processing/mobilenet_preprocess.py:114-160 with :204-206 (float32 accepted) and
+ * imagenet_normalize's float branch, transforms.py:264-267 (divide by 255 only when the
+ * maximum exceeds 1).  crop_dev float [h, w, 3] -> out_chw_dev float [3, out_size, out_size].
+ * The resize is OpenCV's generic float INTER_LINEAR (bit-identical to cv2.resize with IPP
+ * off; pip builds of OpenCV use Intel IPP for float resizes, which differs by up to ~3e-5).
+ * scratch_dev: 16-byte aligned, at least ia_f32_scratch_bytes(out_size) bytes.
+ * ------------------------------------------------------------------------------- */
+size_t ia_f32_scratch_bytes(int out_size);
+int ia_resize_normalize_f32(const float* crop_dev, int h, int w, int out_size, const float mean[3],
+                            const float std[3], float* out_chw_dev, void* scratch_dev,
+                            size_t scratch_bytes, void* stream);
+
+/* imagenet_normalize() on float32 HWC, transforms.py:264-270 -> float HWC.  scratch_dev: 8 bytes. */
+int ia_imagenet_normalize_f32(const float* image_dev, size_t pixels, const float mean[3],
+                              const float std[3], float* out_dev, void* scratch_dev,
+                              size_t scratch_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -153,6 +153,22 @@ __global__ void scale_boxes_kernel(const float* in, int m, int cols, float scale
   out[i] = v;
 }
 
+// scale_boxes on float64 boxes: numpy computes `boxes[:, :4] /= scale` and the clips in the
+// array's own precision (transforms.py:216-228), here binary64 with IEEE _rn operations.
+__global__ void scale_boxes_f64_kernel(const double* in, int m, int cols, double scale, int pad_w,
+                                       int pad_h, int orig_h, int orig_w, double* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m * cols) return;
+  const int c = i % cols;
+  double v = in[i];
+  if (c < 4) {
+    const double t = __ddiv_rn(__dsub_rn(v, (double)((c & 1) ? pad_h : pad_w)), scale);
+    const double hi = (double)((c & 1) ? orig_h : orig_w);
+    v = (t != t) ? t : fmin(fmax(t, 0.0), hi);
+  }
+  out[i] = v;
+}
+
 __global__ void crop_rects_kernel(const float* boxes, int m, int cols, int image_index, int src_h,
                                   int src_w, int* rois) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -185,6 +201,17 @@ extern "C" int ia_scale_boxes(const float* boxes_dev, int m, int cols, float sca
   IA_RETURN_IF(!boxes_dev || !out_dev, IA_ERR_INVALID_ARGUMENT);
   const int total = m * cols;
   ia::scale_boxes_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      boxes_dev, m, cols, scale, pad_w, pad_h, orig_h, orig_w, out_dev);
+  return ia::launch_status();
+}
+
+extern "C" int ia_scale_boxes_f64(const double* boxes_dev, int m, int cols, double scale, int pad_w,
+                                  int pad_h, int orig_h, int orig_w, double* out_dev, void* stream) {
+  IA_RETURN_IF(m < 0 || cols < 4, IA_ERR_INVALID_ARGUMENT);
+  if (m == 0) return IA_OK;
+  IA_RETURN_IF(!boxes_dev || !out_dev, IA_ERR_INVALID_ARGUMENT);
+  const int total = m * cols;
+  ia::scale_boxes_f64_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
       boxes_dev, m, cols, scale, pad_w, pad_h, orig_h, orig_w, out_dev);
   return ia::launch_status();
 }

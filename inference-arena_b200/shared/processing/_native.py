@@ -51,6 +51,8 @@ _SIGNATURES = {
                        c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "ia_scale_boxes": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_int, c_int, c_int,
                                c_void_p, c_void_p]),
+    "ia_scale_boxes_f64": (c_int, [c_void_p, c_int, c_int, c_double, c_int, c_int, c_int, c_int,
+                                   c_void_p, c_void_p]),
     "ia_crop_resize_normalize": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int,
                                          c_float, c_int, c_int, c_int, F3, F3, c_void_p, c_int,
                                          c_void_p, c_void_p, c_void_p]),
@@ -59,6 +61,10 @@ _SIGNATURES = {
     "ia_resize_normalize_rois": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, F3,
                                          F3, c_void_p, c_void_p]),
     "ia_extract_crop_rects": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "ia_f32_scratch_bytes": (c_size_t, [c_int]),
+    "ia_resize_normalize_f32": (c_int, [c_void_p, c_int, c_int, c_int, F3, F3, c_void_p, c_void_p, c_size_t,
+                                        c_void_p]),
+    "ia_imagenet_normalize_f32": (c_int, [c_void_p, c_size_t, F3, F3, c_void_p, c_void_p, c_size_t, c_void_p]),
     "ia_imagenet_normalize_u8": (c_int, [c_void_p, c_size_t, F3, F3, c_void_p, c_void_p]),
 }
 

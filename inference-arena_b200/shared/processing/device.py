@@ -169,6 +169,15 @@ def nms_cuda(boxes: torch.Tensor, scores: torch.Tensor, class_ids: torch.Tensor,
 # ------------------------------------------------------------------------------------- K4
 def scale_boxes_cuda(boxes: torch.Tensor, scale: float, padding, original_shape) -> torch.Tensor:
     """scale_boxes (reference transforms.py:183-230) on a float32 [M, >=4] CUDA tensor."""
+    if isinstance(boxes, torch.Tensor) and boxes.dtype == torch.float64:
+        boxes = _require_cuda(boxes, torch.float64, "boxes")
+        out = torch.empty_like(boxes)
+        m, cols = boxes.shape
+        with torch.cuda.device(boxes.device):
+            check(lib().ia_scale_boxes_f64(boxes.data_ptr(), m, cols, float(scale), int(padding[0]),
+                                           int(padding[1]), int(original_shape[0]), int(original_shape[1]),
+                                           out.data_ptr(), _stream_ptr(boxes.device)), "ia_scale_boxes_f64")
+        return out
     boxes = _require_cuda(boxes, torch.float32, "boxes")
     out = torch.empty_like(boxes)
     m, cols = boxes.shape
@@ -304,3 +313,38 @@ def crop_ragged_cuda(frames: list[torch.Tensor], dets: torch.Tensor, count: torc
             F3(*[float(np.float32(v)) for v in std]), out.data_ptr(), cap, offsets.data_ptr(), rois.data_ptr(),
             _stream_ptr(dev)), "ia_crop_resize_normalize_ragged")
     return out, offsets, rois
+
+
+# --------------------------------------------------------------- float32-input branch (N2)
+def resize_normalize_f32_cuda(crop: torch.Tensor, out_size: int = 224, mean=(0.485, 0.456, 0.406),
+                              std=(0.229, 0.224, 0.225)) -> torch.Tensor:
+    """MobileNetPreprocessor.preprocess on a float32 [H,W,3] CUDA crop (reference
+    mobilenet_preprocess.py:114-160, float branch) -> float32 [1,3,S,S]."""
+    crop = _require_cuda(crop, torch.float32, "crop")
+    h, w, _ = crop.shape
+    dev = crop.device
+    out = torch.empty((1, 3, out_size, out_size), dtype=torch.float32, device=dev)
+    need = lib().ia_f32_scratch_bytes(int(out_size))
+    scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().ia_resize_normalize_f32(crop.data_ptr(), h, w, int(out_size),
+                                            F3(*[float(np.float32(v)) for v in mean]),
+                                            F3(*[float(np.float32(v)) for v in std]), out.data_ptr(),
+                                            scratch.data_ptr(), need, _stream_ptr(dev)), "ia_resize_normalize_f32")
+    return out
+
+
+def imagenet_normalize_f32_cuda(image: torch.Tensor, mean=(0.485, 0.456, 0.406),
+                                std=(0.229, 0.224, 0.225)) -> torch.Tensor:
+    """imagenet_normalize on float32 [..., 3] (reference transforms.py:264-270): divided by 255
+    only when the image's maximum exceeds 1."""
+    image = _require_cuda(image, torch.float32, "image")
+    out = torch.empty_like(image)
+    scratch = torch.empty(16, dtype=torch.uint8, device=image.device)
+    with torch.cuda.device(image.device):
+        check(lib().ia_imagenet_normalize_f32(image.data_ptr(), image.numel() // 3,
+                                              F3(*[float(np.float32(v)) for v in mean]),
+                                              F3(*[float(np.float32(v)) for v in std]), out.data_ptr(),
+                                              scratch.data_ptr(), 16, _stream_ptr(image.device)),
+              "ia_imagenet_normalize_f32")
+    return out

@@ -47,9 +47,11 @@ class MobileNetPreprocessor:
 
     def preprocess(self, crop: np.ndarray) -> MobileNetPreprocessResult:
         self._validate_input(crop)
-        if crop.dtype != np.uint8:
-            raise NotImplementedError("float32 crops are not on the GPU path yet (DESIGN.md §7)")
         height, width = crop.shape[0], crop.shape[1]
+        if crop.dtype == np.float32:  # OpenCV's float resize + the float branch of imagenet_normalize
+            tensor = _dev.resize_normalize_f32_cuda(_hostio.to_device(crop), self.input_size, IMAGENET_MEAN,
+                                                    IMAGENET_STD)
+            return MobileNetPreprocessResult(tensor=_hostio.to_host(tensor), original_shape=(height, width))
         frames = _hostio.to_device(crop)[None]
         rois = _whole_image_rois([(height, width)]).to(frames.device)
         # like the reference (mobilenet_preprocess.py:146 -> transforms.py:270) the module-level

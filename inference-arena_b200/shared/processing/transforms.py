@@ -58,9 +58,8 @@ def scale_boxes(boxes: np.ndarray, scale: float, padding: tuple[int, int],
                 original_shape: tuple[int, int]) -> np.ndarray:
     """Map ``[N, 4+]`` boxes from letterbox space back to the original frame (input is not
     modified; columns past the fourth are passed through)."""
-    if boxes.dtype != np.float32:
-        raise NotImplementedError(
-            f"scale_boxes: float32 boxes only on the GPU path, got {boxes.dtype}")
+    if boxes.dtype not in (np.float32, np.float64):
+        raise TypeError(f"scale_boxes: float32 or float64 boxes expected, got {boxes.dtype}")
     if boxes.shape[0] == 0:
         return boxes.copy()
     out = _dev.scale_boxes_cuda(_hostio.to_device(boxes), scale, padding, original_shape)
@@ -69,8 +68,9 @@ def scale_boxes(boxes: np.ndarray, scale: float, padding: tuple[int, int],
 
 def imagenet_normalize(image: np.ndarray) -> np.ndarray:
     """``(pixel / 255 - mean) / std`` per channel, float32 HWC out."""
-    if image.dtype != np.uint8:
-        raise NotImplementedError(
-            f"imagenet_normalize: uint8 input only on the GPU path, got {image.dtype}")
-    out = _dev.imagenet_normalize_cuda(_hostio.to_device(image), IMAGENET_MEAN, IMAGENET_STD)
+    if image.dtype == np.uint8:
+        out = _dev.imagenet_normalize_cuda(_hostio.to_device(image), IMAGENET_MEAN, IMAGENET_STD)
+    else:  # reference: image.astype(np.float32), rescaled by 1/255 only when its maximum exceeds 1
+        out = _dev.imagenet_normalize_f32_cuda(_hostio.to_device(image.astype(np.float32)), IMAGENET_MEAN,
+                                               IMAGENET_STD)
     return _hostio.to_host(out)

@@ -99,3 +99,45 @@ def resize_linear_u8(img: np.ndarray, dst_w: int, dst_h: int) -> np.ndarray:
     h1 = hrow[r1] >> 4
     out = (((b0[:, None, None] * h0) >> 16) + ((b1[:, None, None] * h1) >> 16) + 2) >> 2
     return np.clip(out, 0, 255).astype(np.uint8)
+
+
+def resize_linear_f32(img: np.ndarray, dst_w: int, dst_h: int) -> np.ndarray:
+    """``cv2.resize(img, (dst_w, dst_h), INTER_LINEAR)`` for float32 HWC — OpenCV's GENERIC
+    float path (resize.cpp ``HResizeLinear<float>`` / ``VResizeLinear<float>``): the same
+    coordinate maths as the 8-bit path, float coefficients ``1 - f`` and ``f``, every product
+    and every sum rounded to float32 on its own (no FMA), horizontal pass first.  An exact
+    2x downscale is the box average ``(((p00 + p01) + p10) + p11) * 0.25``.
+
+    Bit-identical to ``cv2.resize`` with ``cv2.ipp.setUseIPP(False)``.  The pip builds of
+    OpenCV route float resizes through Intel IPP, whose (unpublished) arithmetic differs from
+    this by up to ~3e-5 on [0, 1] data — see tests/test_oracle_cv_resize.py."""
+    assert img.dtype == np.float32 and img.ndim == 3
+    src_h, src_w = img.shape[:2]
+    if (dst_h, dst_w) == (src_h, src_w):
+        return img.copy()
+    if is_box2x(dst_h, dst_w, src_h, src_w):
+        s = img[0::2, 0::2] + img[0::2, 1::2]
+        s = s + img[1::2, 0::2]
+        s = s + img[1::2, 1::2]
+        return (s[:dst_h, :dst_w] * np.float32(0.25)).astype(np.float32)
+
+    def table(dst, src, zero_frac_at_border):
+        sc = 1.0 / (float(dst) / float(src))
+        i = np.arange(dst, dtype=np.float64)
+        f = ((i + 0.5) * sc - 0.5).astype(np.float32)
+        s0 = np.floor(f).astype(np.int32)
+        f = (f - s0.astype(np.float32)).astype(np.float32)
+        if zero_frac_at_border:
+            lo = s0 < 0
+            s0, f = np.where(lo, 0, s0), np.where(lo, np.float32(0), f)
+            hi = s0 >= src - 1
+            s0, f = np.where(hi, src - 1, s0), np.where(hi, np.float32(0), f)
+        return s0, (np.float32(1) - f).astype(np.float32), f.astype(np.float32)
+
+    x0, a0, a1 = table(dst_w, src_w, True)
+    y0, b0, b1 = table(dst_h, src_h, False)
+    x1 = np.minimum(x0 + 1, src_w - 1)
+    r0, r1 = np.clip(y0, 0, src_h - 1), np.clip(y0 + 1, 0, src_h - 1)
+    h = (img[:, x0] * a0[None, :, None]).astype(np.float32) + (img[:, x1] * a1[None, :, None]).astype(np.float32)
+    out = (h[r0] * b0[:, None, None]).astype(np.float32) + (h[r1] * b1[:, None, None]).astype(np.float32)
+    return out.astype(np.float32)

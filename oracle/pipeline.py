@@ -16,7 +16,7 @@ from dataclasses import dataclass
 
 import numpy as np
 
-from .cv_resize import resize_linear_u8
+from .cv_resize import resize_linear_f32, resize_linear_u8
 
 # experiment.yaml:232-245 (controlled_variables.preprocessing) and transforms.py:37
 YOLO_SIZE = 640
@@ -235,10 +235,10 @@ def imagenet_normalize(image: np.ndarray, mean=MEAN, std=STD) -> np.ndarray:
 
 # --------------------------------------------------------------------------- a8
 def mobilenet_preprocess(crop: np.ndarray, size: int = MOBILENET_SIZE, resize=resize_linear_u8):
-    """mobilenet_preprocess.py:114-160 -> float32[1,3,S,S] (uint8 crops)."""
+    """mobilenet_preprocess.py:114-160 -> float32[1,3,S,S] (uint8 or float32 crops)."""
     _check_image(crop, "crop", (np.uint8, np.float32))
-    if crop.dtype != np.uint8:
-        raise NotImplementedError("oracle restates the uint8 crop branch only")
+    if crop.dtype == np.float32 and resize is resize_linear_u8:
+        resize = resize_linear_f32  # :204-206 float crops go through OpenCV's float path
     chw = imagenet_normalize(resize(crop, size, size)).transpose(2, 0, 1)
     return np.ascontiguousarray(chw[None])
 

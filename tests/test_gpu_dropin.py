@@ -141,3 +141,33 @@ def test_end_to_end_like_reference_pipeline(sp):
     crops = np.concatenate([mob(extract_crop(frame, d)).tensor for d in orig], axis=0)
     assert np.array_equal(res.tensor, want_tensor) and np.array_equal(dets, want_dets)
     assert np.array_equal(orig, want_orig) and np.array_equal(crops, want_crops)
+
+
+def test_float32_inputs(sp):
+    """The float32 branch (reference mobilenet_preprocess.py:204-206, transforms.py:264-267;
+    exercised by the reference's test_processing.py:165-170 and :561-573)."""
+    rng = np.random.default_rng(42)
+    p = sp.MobileNetPreprocessor()
+    for shape in ((100, 100), (448, 448), (224, 224), (37, 301)):
+        for scale in (1.0, 255.0):  # [0,1] data stays as is, [0,255] data is divided by 255
+            crop = (rng.random((*shape, 3)) * scale).astype(np.float32)
+            res = p(crop)
+            assert res.tensor.shape == (1, 3, 224, 224) and res.tensor.dtype == np.float32
+            assert np.array_equal(res.tensor, O.mobilenet_preprocess(crop)), (shape, scale)
+    img = rng.random((10, 10, 3)).astype(np.float32)
+    assert np.array_equal(sp.imagenet_normalize(img), O.imagenet_normalize(img))
+    img255 = (img * 255).astype(np.float32)
+    assert np.array_equal(sp.imagenet_normalize(img255), O.imagenet_normalize(img255))
+    with_nan = img.copy()
+    with_nan[0, 0, 0] = np.nan
+    got, want = sp.imagenet_normalize(with_nan), O.imagenet_normalize(with_nan)
+    assert np.array_equal(got, want, equal_nan=True)
+
+
+def test_scale_boxes_float64(sp):
+    boxes = np.array([[320.5, 320.25, 400.75, 400.1, 0.92, 0], [-10, 700, 650, 10, 0.85, 1]], dtype=np.float64)
+    for sc, pad, shape in [(0.3333333333333333, (0, 140), (1080, 1920)), (1.0, (0, 80), (480, 640))]:
+        got = sp.scale_boxes(boxes, sc, pad, shape)
+        assert got.dtype == np.float64 and np.array_equal(got, O.scale_boxes(boxes, sc, pad, shape))
+    with pytest.raises(TypeError):
+        sp.scale_boxes(boxes.astype(np.int32), 1.0, (0, 0), (10, 10))

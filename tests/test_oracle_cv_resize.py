@@ -38,3 +38,22 @@ def test_special_cases():
     # exact 3x downscale lands on pixel centres: pure subsample
     x0, a0, a1 = axis_table(640, 1920, True)
     assert np.array_equal(x0, 3 * np.arange(640) + 1) and (a1 == 0).all() and (a0 == 2048).all()
+
+
+@pytest.mark.parametrize("h,w", [(100, 100), (10, 10), (500, 800), (224, 224), (448, 448), (1, 1), (300, 17), (223, 225)])
+def test_float32_resize_matches_cv2_generic_path(h, w):
+    """Bit-exact against cv2 with IPP off; within 1e-4 of the IPP-accelerated default (the
+    pip wheels' float resize is Intel IPP, whose arithmetic is not OpenCV's published one)."""
+    from oracle.cv_resize import resize_linear_f32
+
+    img = np.random.default_rng(h * 4096 + w).random((h, w, 3)).astype(np.float32)
+    got = resize_linear_f32(img, 224, 224)
+    with_ipp = cv2.resize(img, (224, 224), interpolation=cv2.INTER_LINEAR)
+    was = cv2.ipp.useIPP()
+    try:
+        cv2.ipp.setUseIPP(False)
+        generic = cv2.resize(img, (224, 224), interpolation=cv2.INTER_LINEAR)
+    finally:
+        cv2.ipp.setUseIPP(was)
+    assert np.array_equal(got, generic)
+    assert np.allclose(got, with_ipp, rtol=0, atol=1e-4)
