@@ -71,7 +71,7 @@ def _cpu_worker_init(images: int, seed_base: int) -> None:
     (BASELINE.md §3 mode ii: one process per host core)."""
     import cv2
 
-    from oracle import synth
+    from workloads import synth
 
     cv2.setNumThreads(1)
     seed = seed_base + os.getpid() % 100000
@@ -250,7 +250,7 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
     (algorithmic bytes per SURVEY §8d).  Buffers rotate so no input is re-read from L2."""
     import torch
 
-    from oracle import synth  # seeds/generators only (host side); not on the timed path
+    from workloads import synth  # seeded input generators (host side); not on the timed path
     from shared.processing import device as D
 
     out = {}
@@ -493,7 +493,7 @@ def parity_spot_check(dev) -> str:
     import torch
 
     from oracle import pipeline as O
-    from oracle import synth
+    from workloads import synth
     from shared.processing.pipeline import DevicePipeline
 
     frames = synth.frames(4, SRC_H, SRC_W, seed=77)

@@ -26,7 +26,7 @@ class FakeYolo:
     """Stands in for ModelRegistry.get_session("yolov5n").run (src/shared/model/registry.py)."""
 
     def run(self, _names, feeds):
-        from oracle import synth  # synthetic head generator only (test infrastructure)
+        from workloads import synth  # seeded synthetic head generator
 
         assert feeds["images"].shape == (1, 3, 640, 640) and feeds["images"].dtype == np.float32
         return [synth.head_v5(1, seed=1, objects=4)]

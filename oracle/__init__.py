@@ -18,5 +18,5 @@ Modules
                 (third-party arithmetic the reference calls at
                 transforms.py:160-164 and mobilenet_preprocess.py:139-143)
     pipeline    numpy restatement of the reference functions a1..a9
-    synth       seeded synthetic workloads C1..C5
+    synth       shim for workloads/synth.py (seeded synthetic inputs C1..C5)
 """

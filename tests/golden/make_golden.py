@@ -7,7 +7,7 @@ Run in the build container (the only place ``/root/reference`` exists):
 
 It imports the reference's own modules (``src/shared/processing/*``,
 ``src/shared/data/curator.py``, ``architectures/monolithic/app/postprocess.py``),
-feeds them the seeded inputs of ``oracle/synth.py`` and stores what they return in
+feeds them the seeded inputs of ``workloads/synth.py`` and stores what they return in
 ``golden.npz`` (small arrays verbatim; large tensors as SHA-256 of their bytes plus a
 strided sample).  Nothing at test/bench time reads ``/root/reference``; the tests read
 only the committed ``golden.npz``.
@@ -29,7 +29,7 @@ REF = Path("/root/reference")
 sys.path.insert(0, str(REPO))
 sys.path.insert(0, str(REF / "src"))
 
-from oracle import synth  # noqa: E402
+from workloads import synth  # noqa: E402
 
 LETTERBOX_SHAPES = [(480, 640), (1080, 1920), (1920, 1080), (500, 375), (333, 500), (427, 640),
                     (640, 640), (100, 50), (1281, 1279), (720, 1280), (1280, 1280), (37, 640)]

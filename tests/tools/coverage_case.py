@@ -1,5 +1,5 @@
 import sys
-sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent)); sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent / "inference-arena_b200"))
+sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent.parent)); sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent.parent / "inference-arena_b200"))
 import numpy as np, torch
 from oracle import synth, pipeline as O
 from shared.processing import device as D

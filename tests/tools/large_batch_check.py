@@ -1,7 +1,7 @@
 """Ad-hoc: index arithmetic at large batch (2048 images) — spot-check against the oracle."""
 import sys
 from pathlib import Path
-R = Path(__file__).resolve().parent.parent
+R = Path(__file__).resolve().parent.parent.parent
 sys.path.insert(0, str(R)); sys.path.insert(0, str(R / "inference-arena_b200"))
 import numpy as np, torch
 from oracle import pipeline as O, synth
