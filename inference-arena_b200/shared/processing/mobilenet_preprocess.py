@@ -87,14 +87,14 @@ class MobileNetPreprocessor:
 
 def extract_crop(image: np.ndarray, box: np.ndarray) -> np.ndarray:
     """Copy the region ``box[:4] = [x1, y1, x2, y2]`` (truncated toward zero, clamped to the
-    frame) out of ``image``; an empty region yields ``zeros((1, 1, 3))``.  The rectangle is
-    computed on the device by the code the fused K4 kernel uses; the pixels are a device
-    slice copied back."""
+    frame) out of ``image``; an empty region yields ``zeros((1, 1, 3))``.  The rectangle
+    arithmetic runs on the device (the code the fused K4 kernel uses); the pixels of a host
+    image are then a plain host-side slice copy — moving the whole frame to the GPU and back
+    just to copy a window of it would only add PCIe traffic."""
     height, width = image.shape[:2]
     row = np.asarray(box[:4], dtype=np.float64).astype(np.float32).reshape(1, 4)
-    frame = _hostio.to_device(image)
     rect = _hostio.to_host(_dev.extract_crop_rects_cuda(_hostio.to_device(row), height, width))[0]
     _, x1, y1, x2, y2, empty = (int(v) for v in rect[:6])
     if empty:
         return np.zeros((1, 1, 3), dtype=np.uint8)
-    return _hostio.to_host(frame[y1:y2, x1:x2])
+    return image[y1:y2, x1:x2].copy()
