@@ -1,22 +1,11 @@
 """Drop-in `shared` package: the B200 implementation of Inference Arena's shared
-image-processing path.  Same import surface as the reference's ``src/shared/__init__.py``
-(:15-29) for the processing names; every arithmetic step runs in libia_b200.so on the GPU.
+image-processing path.  Re-exports the processing names the reference's
+``src/shared/__init__.py`` (:15-29) exposes; every arithmetic step runs in libia_b200.so on
+the GPU.
 """
 
-from shared.processing import (
-    MobileNetPreprocessor,
-    YOLOPreprocessor,
-    imagenet_normalize,
-    letterbox,
-    scale_boxes,
-)
-
-__all__ = [
-    "YOLOPreprocessor",
-    "MobileNetPreprocessor",
-    "letterbox",
-    "imagenet_normalize",
-    "scale_boxes",
-]
+import shared.processing as _processing
 
 __version__ = "0.1.0"
+__all__ = ["YOLOPreprocessor", "MobileNetPreprocessor", "letterbox", "imagenet_normalize", "scale_boxes"]
+globals().update({name: getattr(_processing, name) for name in __all__})
