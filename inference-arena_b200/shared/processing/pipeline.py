@@ -52,11 +52,28 @@ class DevicePipeline:
         self.crops = torch.empty((self.roi_capacity, 3, crop_size, crop_size), dtype=torch.float32, device=dev)
         need = D.lib().ia_decode_nms_workspace_bytes(max_batch, anchors, self.max_candidates)
         self.workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+        self._side = None  # side stream for run(overlap=True)
 
-    def run(self, frames: torch.Tensor, head: torch.Tensor, events=None) -> PipelineOutput:
+    def run(self, frames: torch.Tensor, head: torch.Tensor, events=None, overlap: bool = False) -> PipelineOutput:
         """``events``: optional list of 4 CUDA events recorded before K1, before K2, between K3
-        and K4, and after K4 (bench.py's per-kernel timing)."""
+        and K4, and after K4 (bench.py's per-kernel timing).  ``overlap=True`` runs K1 on a
+        side stream next to K2 -> K3 -> K4 (K1 shares no data with them): the latency-bound
+        NMS / ROI kernels then hide behind the bandwidth-bound ones."""
         n = frames.shape[0]
+        if overlap and not events:
+            cur = torch.cuda.current_stream(self.device)
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.device)
+            self._side.wait_stream(cur)
+            with torch.cuda.stream(self._side):
+                tensor = D.preprocess_batch_cuda(frames, self.target, out=self.tensor[:n])
+            dets, keep, count, status = D.decode_nms_cuda(
+                head, self.conf, self.iou, max_candidates=self.max_candidates, max_det=self.max_det,
+                workspace=self.workspace)
+            crops, offsets, rois = D.crop_batch_cuda(frames, dets, count, self.geom, self.crop_size,
+                                                     roi_capacity=self.roi_capacity, out=self.crops)
+            cur.wait_stream(self._side)
+            return PipelineOutput(tensor, dets, keep, count, status, crops, offsets, rois)
         if events:
             events[0].record()
         tensor = D.preprocess_batch_cuda(frames, self.target, out=self.tensor[:n])

@@ -88,3 +88,15 @@ def test_graphed_pipeline_matches_eager():
         out = gp.run(torch.from_numpy(frames).cuda(), torch.from_numpy(heads).cuda())
         torch.cuda.synchronize()
         _check_device(out, _oracle(frames, heads))
+
+
+def test_device_pipeline_overlapped_streams():
+    from shared.processing.pipeline import DevicePipeline
+
+    n, h, w = 4, 480, 640
+    frames, heads = synth.frames(n, h, w, seed=94), synth.head_v5(n, seed=95)
+    pipe = DevicePipeline(n, h, w, "cuda")
+    for _ in range(2):
+        out = pipe.run(torch.from_numpy(frames).cuda(), torch.from_numpy(heads).cuda(), overlap=True)
+    torch.cuda.synchronize()
+    _check_device(out, _oracle(frames, heads))
