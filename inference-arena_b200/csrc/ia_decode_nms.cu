@@ -338,43 +338,87 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsParams p) {
         if (acc_hi) atomicOr(&removed_hi, acc_hi);
       }
     }
-    // ---- phase B: 64x64 suppression bitmask inside the block ---------------------------
-    for (int i = warp; i < nb; i += kNmsWarps) {
-      const int ci = bcls[i];
-      const float ix1 = bx1[i], iy1 = by1[i], ix2 = bx2[i], iy2 = by2[i], ia_ = barea[i];
-      const int j0 = lane, j1 = lane + 32;
-      const bool s0 = j0 > i && j0 < nb && bcls[j0] == ci &&
-                      suppresses(ix1, iy1, ix2, iy2, ia_, bx1[j0], by1[j0], bx2[j0], by2[j0], barea[j0], p.iou_thr);
-      const bool s1 = j1 > i && j1 < nb && bcls[j1] == ci &&
-                      suppresses(ix1, iy1, ix2, iy2, ia_, bx1[j1], by1[j1], bx2[j1], by2[j1], barea[j1], p.iou_thr);
-      const unsigned lo = __ballot_sync(0xffffffffu, s0);
-      const unsigned hi = __ballot_sync(0xffffffffu, s1);
-      if (lane == 0) rowmask[i] = (uint64_t)lo | ((uint64_t)hi << 32);
-    }
     __syncthreads();
 
-    // ---- serial resolve on 64-bit words -----------------------------------------------
-    if (tid == 0) {
+    // ---- phase B: greedy resolve inside the block --------------------------------------
+    // A row of the 64x64 suppression matrix is only needed for a box that is KEPT.  Warp 0
+    // therefore starts on demand: take the first alive candidate, keep it, test it against
+    // the alive candidates behind it (two per lane, one ballot each), clear what it
+    // suppresses.  Images with duplicates around a few objects finish within a few rows.  If
+    // more than kLazyRows boxes of the block are kept (little overlap), the remaining rows are
+    // computed by all warps at once and resolved serially on 64-bit words.
+    constexpr int kLazyRows = 8;
+    if (warp == 0) {
       uint64_t alive = (nb == 64 ? ~0ull : ((1ull << nb) - 1ull)) &
                        ~((uint64_t)removed_lo | ((uint64_t)removed_hi << 32));
       int kc = 0;
       int seg_cls = s_seg_cls, seg_start = s_seg_start;
-      while (alive) {
+      const int j0 = lane, j1 = lane + 32;
+      while (alive && kc < kLazyRows) {
         const int i = __ffsll((long long)alive) - 1;
-        klist[kc] = i;
-        if (bcls[i] != seg_cls) {
-          seg_cls = bcls[i];
+        const int ci = bcls[i];
+        if (lane == 0) klist[kc] = i;
+        if (ci != seg_cls) {
+          seg_cls = ci;
           seg_start = K + kc;
         }
         ++kc;
-        alive &= ~rowmask[i];
+        const float ix1 = bx1[i], iy1 = by1[i], ix2 = bx2[i], iy2 = by2[i], ia_ = barea[i];
+        const bool s0 = j0 > i && ((alive >> j0) & 1ull) && bcls[j0] == ci &&
+                        suppresses(ix1, iy1, ix2, iy2, ia_, bx1[j0], by1[j0], bx2[j0], by2[j0], barea[j0], p.iou_thr);
+        const bool s1 = j1 > i && ((alive >> j1) & 1ull) && bcls[j1] == ci &&
+                        suppresses(ix1, iy1, ix2, iy2, ia_, bx1[j1], by1[j1], bx2[j1], by2[j1], barea[j1], p.iou_thr);
+        const unsigned lo = __ballot_sync(0xffffffffu, s0);
+        const unsigned hi = __ballot_sync(0xffffffffu, s1);
+        alive &= ~((uint64_t)lo | ((uint64_t)hi << 32));
         alive &= ~(1ull << i);
       }
-      s_kcount = kc;
-      s_seg_cls = seg_cls;
-      s_seg_start = seg_start;
+      if (lane == 0) {
+        s_kcount = kc;
+        s_seg_cls = seg_cls;
+        s_seg_start = seg_start;
+        removed_lo = (unsigned)alive;  // re-used: the candidates still undecided
+        removed_hi = (unsigned)(alive >> 32);
+      }
     }
     __syncthreads();
+    const uint64_t pending = (uint64_t)removed_lo | ((uint64_t)removed_hi << 32);
+    if (pending) {  // uniform: the rest of the block in parallel
+      for (int i = warp; i < nb; i += kNmsWarps) {
+        if (!((pending >> i) & 1ull)) continue;
+        const int ci = bcls[i];
+        const float ix1 = bx1[i], iy1 = by1[i], ix2 = bx2[i], iy2 = by2[i], ia_ = barea[i];
+        const int j0 = lane, j1 = lane + 32;
+        const bool s0 = j0 > i && ((pending >> j0) & 1ull) && bcls[j0] == ci &&
+                        suppresses(ix1, iy1, ix2, iy2, ia_, bx1[j0], by1[j0], bx2[j0], by2[j0], barea[j0], p.iou_thr);
+        const bool s1 = j1 > i && ((pending >> j1) & 1ull) && bcls[j1] == ci &&
+                        suppresses(ix1, iy1, ix2, iy2, ia_, bx1[j1], by1[j1], bx2[j1], by2[j1], barea[j1], p.iou_thr);
+        const unsigned lo = __ballot_sync(0xffffffffu, s0);
+        const unsigned hi = __ballot_sync(0xffffffffu, s1);
+        if (lane == 0) rowmask[i] = (uint64_t)lo | ((uint64_t)hi << 32);
+      }
+      __syncthreads();
+      if (tid == 0) {
+        uint64_t alive = pending;
+        int kc = s_kcount;
+        int seg_cls = s_seg_cls, seg_start = s_seg_start;
+        while (alive) {
+          const int i = __ffsll((long long)alive) - 1;
+          klist[kc] = i;
+          if (bcls[i] != seg_cls) {
+            seg_cls = bcls[i];
+            seg_start = K + kc;
+          }
+          ++kc;
+          alive &= ~rowmask[i];
+          alive &= ~(1ull << i);
+        }
+        s_kcount = kc;
+        s_seg_cls = seg_cls;
+        s_seg_start = seg_start;
+      }
+      __syncthreads();
+    }
 
     // ---- append the kept rows (postprocess.py:56-73) ----------------------------------
     const int kc = s_kcount;
