@@ -239,9 +239,12 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
     const int buf = s & 1;
     mbar_wait(&full[buf], (s >> 1) & 1);
     if (cur.sb == 0) {
-      ++n_item;
       if (!cur.empty) {
-        // x table of this ROI (double-buffered by item parity), then a consumers-only barrier
+        // x table of this ROI, double-buffered by the parity of the NON-EMPTY items (an empty
+        // ROI has no table and no barrier, so it must not flip the parity), then a
+        // consumers-only barrier: a warp can only overwrite a table two barriers after the
+        // slowest warp last read it
+        ++n_item;
         int2* xt_w = reinterpret_cast<int2*>(xoff + (n_item & 1) * 8 * xg);
         const double sc_x = scx[buf];
         for (int x = tid; x < S; x += kCropConsumers) {

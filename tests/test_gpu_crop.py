@@ -155,3 +155,27 @@ def test_unaligned_frame_buffer_corners(D):
         crops, offsets, _ = D.crop_batch_cuda(frames, _dev(dets), _dev(count), g)
         want = _oracle_crops(frames_np, dets, count, g)
         assert np.array_equal(crops[:4].cpu().numpy(), want), off
+
+
+def test_empty_rois_interleaved_with_real_ones(D):
+    """Many ROIs, every other one empty, more work items than resident CTAs: persistent CTAs
+    alternate between empty items (no staging, no x table) and real ones."""
+    n, h, w, kmax = 16, 480, 640, 8
+    frames = synth.frames(n, h, w, seed=12)
+    dets, _ = synth.detections(n, seed=35, kmax=kmax)
+    rng = np.random.default_rng(3)
+    for i in range(n):
+        for k in range(kmax):
+            if k % 2 == 1:  # empty: x2 <= x1 after truncation
+                dets[i, k, :4] = [100.2, 90.0, 100.9, 300.0]
+            else:
+                c = rng.uniform(60, 580, size=2)
+                wh = rng.uniform(30, 300, size=2)
+                dets[i, k, :4] = [c[0] - wh[0] / 2, c[1] - wh[1] / 2, c[0] + wh[0] / 2, c[1] + wh[1] / 2]
+    count = np.full((n,), kmax, dtype=np.int32)
+    geom = D.letterbox_geometry(h, w, 640)
+    for _ in range(3):
+        crops, offsets, rois = D.crop_batch_cuda(_dev(frames), _dev(dets), _dev(count), geom)
+    want = _oracle_crops(frames, dets, count, geom)
+    assert int(rois[:, 5].sum()) >= n * kmax // 2
+    assert np.array_equal(crops.cpu().numpy(), want)
