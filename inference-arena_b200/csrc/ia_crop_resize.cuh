@@ -1,25 +1,26 @@
 // ia_crop_resize.cuh — K4 stage B: ROI resize + normalise + CHW.
 // Warp-specialised, double-buffered, persistent.
 //
-// Work is a stream of steps; a step is a sub-band (<= 16 output rows, sized to one staging
-// buffer) of one ROI.  CTAs are persistent (grid = SMs x resident CTAs) and stride over the
-// (ROI, band) items; the ROI total is read from device memory, so nothing returns to the
-// host between NMS and here.  A CTA is 7 consumer warps + 1 producer warp, coupled only by
-// mbarriers (full[2] / empty[2]) — no CTA-wide barrier in the loop:
+// Work is a stream of steps; a step is up to 7 output rows (half of a 14-row band, fewer when
+// the crop rows are too wide for one staging buffer) of one ROI.  CTAs are persistent
+// (grid = SMs x resident CTAs) and stride over the (ROI, band) items; the ROI total is read
+// from device memory, so nothing returns to the host between NMS and here.  A CTA is
+// 7 consumer warps + 1 producer warp, coupled only by mbarriers (full / empty per staging
+// buffer) — no CTA-wide barrier in the loop:
 //   producer: lane (row j, tap) evaluates OpenCV's yofs/beta entry, duplicates are removed
-//           with __match_any_sync, the row plan is published, and each distinct crop row
-//           segment is pulled into the free staging buffer with one 1-D bulk async copy (TMA
-//           engine, complete_tx on full[buf]) of its 16-byte-aligned superset, clamped to the
-//           frame buffer (bytes a clamp cuts off are copied by the lane).  It runs up to two
-//           steps ahead of the math.
-//   consumers: 4 consecutive pixels x 3 channels per lane.  The 6 source bytes of a pixel's
-//           two taps come from three aligned 32-bit shared loads + a funnel shift; a PRMT
-//           pairs (p[c], p[c+3]) and one IDP.2A does p0*a0 + p1*a1 against the packed
+//           with __match_any_sync and the copy geometry is worked out — all before waiting
+//           for the consumers to release the buffer; then the row plan is published and each
+//           distinct crop row segment is pulled into the staging buffer with one 1-D bulk
+//           async copy (TMA engine, complete_tx on full[buf]) of its 16-byte-aligned superset,
+//           clamped to the frame buffer (bytes a clamp cuts off are copied by the lane).
+//   consumers: one output row per warp, lanes over consecutive pixels.  The 6 source bytes of
+//           a pixel's two taps come from three aligned 32-bit shared loads + a funnel shift; a
+//           PRMT pairs (p[c], p[c+3]) and one IDP.2A does p0*a0 + p1*a1 against the packed
 //           coefficient pair — OpenCV's 11-bit fixed point, bit-identical to cv2.resize
 //           INTER_LINEAR (copy and the exact-2x box average use the same arithmetic with
 //           tables a0=b0=2048 resp. a0=a1=b0=b1=1024, which reduce to the identity and to
 //           (p00+p01+p10+p11+2)>>2).  Then the ((v/255 - mean)/std) LUT, replicated 4x across
-//           banks, and three 128-bit streaming plane stores.
+//           banks, and one 128-byte streaming store per warp and colour plane.
 // The global side sees only wide, fully used requests; byte gathers hit shared memory.
 #pragma once
 
@@ -27,8 +28,8 @@
 
 namespace ia {
 
-// 7 consumer warps: 224 lanes = 4 output rows x 56 four-pixel groups at out_size 224, so an
-// 8-row step is exactly two full passes (no idle lanes); + 1 producer warp = 256 threads.
+// 7 consumer warps (one output row each per 7-row step; 224 = 7 x 32 pixels per row at
+// out_size 224, so no lane idles) + 1 producer warp = 256 threads.
 constexpr int kCropConsumers = 224;
 constexpr int kCropThreads = kCropConsumers + 32;
 constexpr int kBandRows = 14;  // two 7-row steps per band: one output row per consumer warp
