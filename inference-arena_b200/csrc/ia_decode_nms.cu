@@ -171,6 +171,47 @@ __global__ void __launch_bounds__(kDecodeThreads) decode_filter_v8_kernel(const 
   compact_append(pass, key, p.counts + img, p.keys + (size_t)img * p.key_pitch, p.cap);
 }
 
+// Same, four consecutive anchors per thread: 128-bit loads (a warp reads 512 contiguous bytes
+// of a channel row) and four independent max/arg-max chains.  Needs anchors % 4 == 0 and a
+// 16-byte aligned head (the host falls back to the scalar kernel otherwise).
+__global__ void __launch_bounds__(kDecodeThreads) decode_filter_v8x4_kernel(const DecodeParams p) {
+  const int img = blockIdx.x / p.tiles;
+  const int tile = blockIdx.x - img * p.tiles;
+  const int a = (tile * kDecodeThreads + threadIdx.x) * 4;
+  const float* g = p.head + (size_t)img * p.row_floats * p.anchors;
+  bool pass[4] = {false, false, false, false};
+  float best[4] = {0.f, 0.f, 0.f, 0.f};
+  int best_c[4] = {0, 0, 0, 0};
+  if (a < p.anchors) {
+    const float4* col = reinterpret_cast<const float4*>(g + (size_t)4 * p.anchors + a);
+    const size_t pitch4 = (size_t)p.anchors >> 2;
+    const float4 v0 = __ldg(col);
+    best[0] = v0.x, best[1] = v0.y, best[2] = v0.z, best[3] = v0.w;
+    bool has_nan[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) has_nan[k] = best[k] != best[k];
+#pragma unroll 8
+    for (int c = 1; c < p.classes; ++c) {
+      const float4 q = __ldg(col + (size_t)c * pitch4);
+      const float v[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        has_nan[k] |= (v[k] != v[k]);
+        if (v[k] > best[k]) {
+          best[k] = v[k];
+          best_c[k] = c;
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) pass[k] = !has_nan[k] && (best[k] >= p.conf_thr);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    compact_append(pass[k], make_key(best_c[k], best[k], a + k), p.counts + img,
+                   p.keys + (size_t)img * p.key_pitch, p.cap);
+}
+
 // -------------------------------------------------- filter for already-decoded arrays
 struct FilterParams {
   const float* scores;
@@ -541,11 +582,13 @@ extern "C" int ia_decode_nms(const float* head_dev, int layout, int n, int ancho
     q.comp_stride = 1;
   } else {
     d.row_floats = 4 + num_classes;
-    d.tile_anchors = kDecodeThreads;
-    d.tiles = (anchors + kDecodeThreads - 1) / kDecodeThreads;
+    const bool vec4 = (anchors & 3) == 0 && ((uintptr_t)head_dev & 15) == 0;
+    d.tile_anchors = vec4 ? 4 * kDecodeThreads : kDecodeThreads;
+    d.tiles = (anchors + d.tile_anchors - 1) / d.tile_anchors;
     const long long blocks = (long long)d.tiles * n;
     IA_RETURN_IF(blocks > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
-    decode_filter_v8_kernel<<<(unsigned)blocks, kDecodeThreads, 0, stream>>>(d);
+    if (vec4) decode_filter_v8x4_kernel<<<(unsigned)blocks, kDecodeThreads, 0, stream>>>(d);
+    else decode_filter_v8_kernel<<<(unsigned)blocks, kDecodeThreads, 0, stream>>>(d);
     q.image_stride = (size_t)anchors * d.row_floats;
     q.anchor_stride = 1;
     q.comp_stride = anchors;

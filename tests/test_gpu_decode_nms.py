@@ -117,6 +117,30 @@ def test_v8_layout(D, golden):
     _check(h8, dets, keep, count, status, conf=0.5, iou=0.45, detect=O.detect_v8)
 
 
+def test_v8_scalar_and_vector_kernels_agree(D):
+    """Anchor counts off the 4-anchor vector width take the scalar kernel; both must match the
+    oracle, also with NaN class scores and ragged last tiles."""
+    for anchors in (3, 130, 513, 1001, 1024, 2052):
+        head5 = synth.head_v5_dense(2, seed=50 + anchors, candidates=min(anchors, 60), anchors=anchors)
+        h8 = synth.head_v8_from_v5(head5)
+        h8[1, 4 + 3, anchors // 2] = np.nan
+        _check(h8, *_run(D, h8, conf=0.5, iou=0.45, layout="v8", max_det=anchors), conf=0.5, iou=0.45,
+               detect=O.detect_v8)
+
+
+def test_v8_unaligned_head_pointer(D):
+    """A head whose base address is only 4-byte aligned must not take the 128-bit load path."""
+    head5 = synth.head_v5(1, seed=61, anchors=8400)
+    h8 = synth.head_v8_from_v5(head5)
+    flat = torch.empty(h8.size + 1, dtype=torch.float32, device="cuda")
+    view = flat[1:].view(h8.shape)
+    view.copy_(torch.from_numpy(h8))
+    dets, keep, count, status = D.decode_nms_cuda(view, 0.5, 0.45, layout="v8")
+    torch.cuda.synchronize()
+    _check(h8, dets.cpu().numpy(), keep.cpu().numpy(), count.cpu().numpy(), status.cpu().numpy(),
+           conf=0.5, iou=0.45, detect=O.detect_v8)
+
+
 def test_apply_nms_entry(D):
     """ia_nms on decoded arrays == oracle nms (postprocess.py:76-160 signature)."""
     head = synth.head_v5_dense(1, seed=26, candidates=700, anchors=1500, used_classes=5)
