@@ -320,6 +320,17 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
     ms = time_loop(lambda: D.crop_batch_cuda(frames, dets, count, geom, out=crops), steps, warmup, dev)
     out["C4_crop_512img"] = {"images_per_s": 512 / ms * 1e3, "rois": len(r), "ms": ms, "algorithmic_bytes": by,
                              "achieved_gbs": by / ms / 1e6, "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
+    del frames, crops
+    # ---- N4: softmax + top-5 of MobileNetV2 logits — one C5 step's worth of crops
+    # (launch-bound) and a batch larger than L2 (HBM-bound); algorithmic bytes = the logits read
+    for rows in (1035, 65536):
+        lg = torch.randn((rows, 1000), device=dev) * 4
+        ms = time_loop(lambda: D.classify_topk_cuda(lg, 5), steps, warmup, dev)
+        by = rows * 1000 * 4
+        out[f"N4_softmax_top5_{rows}x1000"] = {"rows_per_s": rows / ms * 1e3, "ms": ms, "algorithmic_bytes": by,
+                                               "achieved_gbs": by / ms / 1e6,
+                                               "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
+        del lg
     return out
 
 

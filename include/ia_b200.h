@@ -230,6 +230,24 @@ int ia_imagenet_normalize_f32(const float* image_dev, size_t pixels, const float
                               const float std[3], float* out_dev, void* scratch_dev,
                               size_t scratch_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------
+ * Classifier logits (the step after the path).
+ *   softmax != 0: ClassificationInference.classify,
+ *     architectures/microservices/classification/app/inference.py:112-132 --
+ *     probs = exp(s - max(s)) / sum, the k largest in argsort(probs)[::-1] order
+ *     (low_index_first = 0: among equal values the larger index comes first, what a
+ *     stable ascending sort reversed gives; the reference's unstable sort leaves ties open).
+ *   softmax == 0, k = 1, low_index_first = 1: np.argmax + the raw value,
+ *     architectures/monolithic/app/inference.py:201-202, triton/gateway/app/pipeline.py:181-182.
+ * logits_dev float [rows, classes] -> ids_dev int32 [rows, k], values_dev float [rows, k],
+ * status_dev int32 [rows] (may be NULL; bit 0 = the row holds a NaN, every probability is
+ * then NaN as in numpy).  NaN orders above +inf (numpy's sort order).  1 <= k <= classes;
+ * classes * 4 bytes must fit one CTA's shared memory (<= 51200 classes), else IA_ERR_UNSUPPORTED.
+ * ------------------------------------------------------------------------------- */
+int ia_classify_topk(const float* logits_dev, int rows, int classes, int k, int softmax,
+                     int low_index_first, int32_t* ids_dev, float* values_dev,
+                     int32_t* status_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

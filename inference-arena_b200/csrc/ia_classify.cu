@@ -1,0 +1,233 @@
+// ia_classify.cu — SURVEY §8f row N4: what the reference does to the classifier's logits.
+//
+//   softmax + top-k   architectures/microservices/classification/app/inference.py:112-132
+//                     exp(s - max(s)) / sum(...), argsort(probs)[::-1][:k]
+//   arg-max + value   architectures/monolithic/app/inference.py:201-202 and
+//                     architectures/triton/gateway/app/pipeline.py:181-182
+//
+// One warp per row of logits.  The row is staged in shared memory once (the only DRAM
+// traffic: classes * 4 bytes per row) and exponentiated in place with the float32 operations
+// numpy performs (subtract, exp; the sum is accumulated in double and rounded once, which
+// lies within one float32 ulp of numpy's pairwise sum).  Taking the k largest must not cost k
+// passes over the row, so the warp first finds a bound: the k-th largest of the 32 per-lane
+// maxima is <= the k-th largest element, hence every winner is >= it.  One more pass
+// compacts the few elements above that bound (typically k..2k of them) with ballots, only
+// those are divided by the sum, and the order among them is settled by k warp-wide maxima of
+// a 64-bit key (ordered value bits : index).  Rows where that shortcut does not apply (NaN or
+// infinite logits, masses of equal values, k > 32) take k plain passes instead.
+#include <math_constants.h>
+
+#include "ia_common.cuh"
+
+namespace ia {
+
+constexpr int kClassifyMaxWarps = 8;
+constexpr size_t kClassifySmemBudget = 96 * 1024;   // per CTA, keeps >= 2 CTAs per SM
+constexpr size_t kClassifySmemLimit = 200 * 1024;   // one row must fit
+
+struct ClassifyParams {
+  const float* logits;
+  int rows, classes, k;
+  int softmax;          // 1: softmax probabilities; 0: raw values
+  int low_index_first;  // tie rule: 0 = argsort()[::-1] of a stable sort, 1 = np.argmax
+  int warps;
+  int32_t* ids;
+  float* values;
+  int32_t* status;
+};
+
+// float -> uint32 whose unsigned order is numpy's sort order: -inf < ... < -0 == +0 < ... <
+// +inf < NaN (NaNs sort last, so they come first in argsort()[::-1] and win np.argmax).
+__device__ __forceinline__ uint32_t order_bits(float x) {
+  if (x != x) return 0xffffffffu;
+  if (x == 0.f) return 0x80000000u;
+  const uint32_t b = __float_as_uint(x);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+__device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const uint64_t o = __shfl_xor_sync(0xffffffffu, v, d);
+    v = o > v ? o : v;
+  }
+  return v;
+}
+
+constexpr int kCandidates = 64;  // per row, fast path
+
+template <bool kSoftmax>
+__global__ void __launch_bounds__(kClassifyMaxWarps * 32) classify_topk_kernel(const ClassifyParams p) {
+  extern __shared__ float rows_smem[];
+  __shared__ uint64_t cand_smem[kClassifyMaxWarps][kCandidates];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * p.warps + warp;
+  if (row >= p.rows) return;  // whole warps leave; no CTA-wide barrier below
+  float* v = rows_smem + (size_t)warp * p.classes;
+  uint64_t* cand = cand_smem[warp];
+  const float* g = p.logits + (size_t)row * p.classes;
+  const int C = p.classes, k = p.k;
+  const uint32_t flip = p.low_index_first ? 0xffffffffu : 0u;
+  constexpr uint32_t kFull = 0xffffffffu;
+
+  // pass A: stage the row, row maximum (np.max: NaN if any NaN)
+  float m = -CUDART_INF_F;
+  bool has_nan = false;
+#pragma unroll 4
+  for (int i = lane; i < C; i += 32) {
+    const float x = __ldg(g + i);
+    v[i] = x;
+    has_nan |= (x != x);
+    m = fmaxf(m, x);  // ignores NaN; restored below
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
+  has_nan = __any_sync(kFull, has_nan);
+
+  // pass B: exp in place + sum (softmax) / nothing (raw); per-lane maximum of the ordered bits
+  uint32_t lane_max = 0;
+  float total = 0.f;
+  bool slow = k > 32;
+  if (kSoftmax) {
+    if (has_nan) m = CUDART_NAN_F;
+    double acc = 0.0;
+    bool bad = false;
+#pragma unroll 4
+    for (int i = lane; i < C; i += 32) {
+      const float e = expf(__fsub_rn(v[i], m));
+      v[i] = e;
+      acc += (double)e;
+      bad |= (e != e);
+      lane_max = max(lane_max, __float_as_uint(e));  // e >= 0: the raw bits are ordered
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(kFull, acc, d);
+    total = (float)acc;
+    slow |= __any_sync(kFull, bad);
+  } else {
+#pragma unroll 4
+    for (int i = lane; i < C; i += 32) lane_max = max(lane_max, order_bits(v[i]));
+  }
+  __syncwarp();
+
+  // bound: k-th largest lane maximum (lanes without elements hold 0, below every real value)
+  uint32_t bound = 0;
+  if (!slow) {
+    bool alive = true;
+    for (int j = 0; j < k; ++j) {
+      bound = __reduce_max_sync(kFull, alive ? lane_max : 0u);
+      const uint32_t owners = __ballot_sync(kFull, alive && lane_max == bound);
+      if (owners && lane == __ffs(owners) - 1) alive = false;
+    }
+    if (kSoftmax) {
+      // p = e / total can round two different e to one p only if they are neighbours, so a
+      // relative margin keeps every element that could tie with a winner; where p would be
+      // denormal the margin argument fails -> plain passes
+      const float e_bound = __uint_as_float(bound);
+      slow = !(e_bound >= 1e-30f);
+      bound = __float_as_uint(__fmul_rn(e_bound, 0.999999f));
+    }
+  }
+
+  int found = 0;
+  if (!slow) {
+    for (int base = 0; base < C; base += 32) {
+      const int i = base + lane;
+      bool is_cand = false;
+      float x = 0.f;
+      if (i < C) {
+        x = v[i];
+        is_cand = (kSoftmax ? __float_as_uint(x) : order_bits(x)) >= bound;
+      }
+      const uint32_t mask = __ballot_sync(kFull, is_cand);
+      if (mask) {
+        const int pos = found + __popc(mask & ((1u << lane) - 1u));
+        if (is_cand && pos < kCandidates) {
+          const float val = kSoftmax ? __fdiv_rn(x, total) : x;
+          cand[pos] = ((uint64_t)order_bits(val) << 32) | ((uint32_t)i ^ flip);
+        }
+        found += __popc(mask);
+      }
+    }
+    slow = found > kCandidates;
+    __syncwarp();
+  }
+
+  if (!slow) {
+    uint64_t c0 = lane < found ? cand[lane] : 0ull;
+    uint64_t c1 = lane + 32 < found ? cand[lane + 32] : 0ull;
+    uint64_t prev = ~0ull;
+    for (int j = 0; j < k; ++j) {
+      const uint64_t a = c0 < prev ? c0 : 0ull, b = c1 < prev ? c1 : 0ull;
+      prev = warp_max_u64(a > b ? a : b);
+      if (lane == 0) {
+        const int idx = (int)((uint32_t)prev ^ flip);
+        p.ids[(size_t)row * k + j] = idx;
+        p.values[(size_t)row * k + j] = kSoftmax ? __fdiv_rn(v[idx], total) : v[idx];
+      }
+    }
+  } else {
+    if (kSoftmax) {
+      for (int i = lane; i < C; i += 32) v[i] = __fdiv_rn(v[i], total);
+      __syncwarp();
+    }
+    uint64_t prev = ~0ull;
+    for (int j = 0; j < k; ++j) {
+      uint64_t best = 0;
+      for (int i = lane; i < C; i += 32) {
+        const uint64_t key = ((uint64_t)order_bits(v[i]) << 32) | ((uint32_t)i ^ flip);
+        if (key < prev && key > best) best = key;
+      }
+      best = warp_max_u64(best);
+      prev = best;
+      if (lane == 0) {
+        const int idx = (int)((uint32_t)best ^ flip);
+        p.ids[(size_t)row * k + j] = idx;
+        p.values[(size_t)row * k + j] = v[idx];
+      }
+    }
+  }
+  if (lane == 0 && p.status) p.status[row] = has_nan ? 1 : 0;
+}
+
+}  // namespace ia
+
+extern "C" int ia_classify_topk(const float* logits_dev, int rows, int classes, int k, int softmax,
+                                int low_index_first, int32_t* ids_dev, float* values_dev,
+                                int32_t* status_dev, void* stream_) {
+  using namespace ia;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IA_RETURN_IF(rows < 0 || classes < 1 || k < 1 || k > classes, IA_ERR_INVALID_ARGUMENT);
+  if (rows == 0) return IA_OK;
+  IA_RETURN_IF(!logits_dev || !ids_dev || !values_dev, IA_ERR_INVALID_ARGUMENT);
+  const size_t row_bytes = (size_t)classes * sizeof(float);
+  IA_RETURN_IF(row_bytes > kClassifySmemLimit, IA_ERR_UNSUPPORTED);
+  int warps = (int)(kClassifySmemBudget / row_bytes);
+  warps = warps < 1 ? 1 : (warps > kClassifyMaxWarps ? kClassifyMaxWarps : warps);
+  const size_t smem = row_bytes * warps;
+  if (smem > 48 * 1024) {
+    static thread_local int raised_for = -1;  // per device, per thread: the attribute is sticky
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (raised_for != dev) {
+      e = cudaFuncSetAttribute(classify_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)kClassifySmemLimit);
+      if (e != cudaSuccess) return (int)e;
+      e = cudaFuncSetAttribute(classify_topk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)kClassifySmemLimit);
+      if (e != cudaSuccess) return (int)e;
+      raised_for = dev;
+    }
+  }
+  ClassifyParams p;
+  p.logits = logits_dev;
+  p.rows = rows, p.classes = classes, p.k = k;
+  p.softmax = softmax != 0, p.low_index_first = low_index_first != 0;
+  p.warps = warps;
+  p.ids = ids_dev, p.values = values_dev, p.status = status_dev;
+  const int blocks = (rows + warps - 1) / warps;
+  if (p.softmax) classify_topk_kernel<true><<<blocks, warps * 32, smem, stream>>>(p);
+  else classify_topk_kernel<false><<<blocks, warps * 32, smem, stream>>>(p);
+  return launch_status();
+}

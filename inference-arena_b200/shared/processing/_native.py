@@ -66,6 +66,8 @@ _SIGNATURES = {
                                         c_void_p]),
     "ia_imagenet_normalize_f32": (c_int, [c_void_p, c_size_t, F3, F3, c_void_p, c_void_p, c_size_t, c_void_p]),
     "ia_imagenet_normalize_u8": (c_int, [c_void_p, c_size_t, F3, F3, c_void_p, c_void_p]),
+    "ia_classify_topk": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                 c_void_p]),
 }
 
 _lib = None

@@ -348,3 +348,27 @@ def imagenet_normalize_f32_cuda(image: torch.Tensor, mean=(0.485, 0.456, 0.406),
                                               scratch.data_ptr(), 16, _stream_ptr(image.device)),
               "ia_imagenet_normalize_f32")
     return out
+
+
+# ------------------------------------------------------------------ classifier logits (N4)
+def classify_topk_cuda(logits: torch.Tensor, k: int = 5, softmax: bool = True,
+                       low_index_first: bool = False) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """float32 [R, C] CUDA logits -> (ids int32 [R,k], values float32 [R,k], status int32 [R]).
+
+    ``softmax=True``: the probabilities and order of ClassificationInference.classify (reference
+    architectures/microservices/classification/app/inference.py:112-118).  ``softmax=False, k=1,
+    low_index_first=True``: np.argmax and the raw value (monolithic/app/inference.py:201-202).
+    ``status`` bit 0: the row holds a NaN."""
+    logits = _require_cuda(logits, torch.float32, "logits")
+    if logits.ndim != 2:
+        raise ValueError(f"logits must be [rows, classes], got {tuple(logits.shape)}")
+    rows, classes = logits.shape
+    dev = logits.device
+    ids = torch.empty((rows, k), dtype=torch.int32, device=dev)
+    values = torch.empty((rows, k), dtype=torch.float32, device=dev)
+    status = torch.empty((rows,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().ia_classify_topk(logits.data_ptr(), rows, classes, int(k), int(bool(softmax)),
+                                     int(bool(low_index_first)), ids.data_ptr(), values.data_ptr(),
+                                     status.data_ptr(), _stream_ptr(dev)), "ia_classify_topk")
+    return ids, values, status

@@ -243,6 +243,25 @@ def mobilenet_preprocess(crop: np.ndarray, size: int = MOBILENET_SIZE, resize=re
     return np.ascontiguousarray(chw[None])
 
 
+# ------------------------------------------------------- classifier logits
+def softmax_topk(scores: np.ndarray, top_k: int = 5):
+    """``ClassificationInference.classify``'s arithmetic,
+    architectures/microservices/classification/app/inference.py:112-118, on one score vector:
+    returns (indices, probabilities of those indices).  The reference's ``argsort`` is an
+    unstable sort, so equal probabilities have no defined order there; a stable sort is used
+    here (reversed: the larger index first) and the synthetic logits are tie-free at the top."""
+    exp_scores = np.exp(scores - np.max(scores))
+    probs = exp_scores / exp_scores.sum()
+    idx = np.argsort(probs, kind="stable")[::-1][:top_k]
+    return idx.astype(np.int64), probs[idx]
+
+
+def top1(cls_output: np.ndarray):
+    """``architectures/monolithic/app/inference.py:201-202``: arg-max and the raw value."""
+    class_id = int(np.argmax(cls_output[0]))
+    return class_id, float(cls_output[0, class_id])
+
+
 # --------------------------------------------------------------------- the chain
 def run_image(frame: np.ndarray, head_image: np.ndarray, conf_thr: float, iou_thr: float,
               resize=resize_linear_u8):

@@ -6,7 +6,8 @@ Run in the build container (the only place ``/root/reference`` exists):
     python tests/golden/make_golden.py
 
 It imports the reference's own modules (``src/shared/processing/*``,
-``src/shared/data/curator.py``, ``architectures/monolithic/app/postprocess.py``),
+``src/shared/data/curator.py``, ``architectures/monolithic/app/postprocess.py``,
+``architectures/microservices/classification/app/inference.py``),
 feeds them the seeded inputs of ``workloads/synth.py`` and stores what they return in
 ``golden.npz`` (small arrays verbatim; large tensors as SHA-256 of their bytes plus a
 strided sample).  Nothing at test/bench time reads ``/root/reference``; the tests read
@@ -174,6 +175,39 @@ def main() -> None:
     out["c1_dets_orig"] = dets_orig
     meta["c1"] = {"tensor_sha": sha(res.tensor), "crops_sha": [sha(c) for c in crops]}
     out["c1_crop_samples"] = np.stack([sample(c) for c in crops])
+
+    # ---- N4: softmax/top-k and arg-max through the reference's own classify() ----------
+    # ClassificationInference is built without __init__ (that needs onnxruntime and a model
+    # file); the session is a stub that returns the seeded logits, so every line of
+    # classify() after session.run — inference.py:112-134 — runs unmodified.
+    sys.path.insert(0, str(REF / "architectures/microservices/classification"))
+    from app.inference import ClassificationInference
+
+    class _Session:
+        def __init__(self, row):
+            self.row = row
+
+        def run(self, _names, _feed):
+            return [self.row[None]]
+
+    class _Pre:
+        tensor = None
+
+    logits = synth.logits(16, seed=400)
+    small = synth.logits(4, seed=401, classes=10)
+    for name, rows, k in (("cls", logits, 5), ("cls_small", small, 3), ("cls_k1", logits[:4], 1)):
+        ids, probs = [], []
+        for row in rows:
+            eng = object.__new__(ClassificationInference)
+            eng.preprocessor = lambda crop: _Pre
+            eng.mobilenet_session = _Session(row)
+            eng.labels = [str(i) for i in range(rows.shape[1])]
+            top_id, _, top_conf, top = eng.classify(None, top_k=k)
+            assert top[0][0] == top_id and top[0][2] == top_conf
+            ids.append([t[0] for t in top])
+            probs.append([t[2] for t in top])
+        out[f"{name}_ids"] = np.array(ids, dtype=np.int64)
+        out[f"{name}_probs"] = np.array(probs, dtype=np.float64)  # float(probs[idx]) of f32 values
 
     out["meta_json"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
     np.savez_compressed(HERE / "golden.npz", **out)

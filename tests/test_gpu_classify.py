@@ -1,0 +1,117 @@
+"""N4 parity: softmax + top-k / arg-max of classifier logits on the GPU vs the oracle and the
+vectors the reference's own classify() produced.  Class indices: exact.  Probabilities:
+1e-5 relative (measured ~1e-7 — CUDA's expf and numpy's differ in the last bit)."""
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pipeline as O
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def D():
+    from shared.processing import device
+    return device
+
+
+def _run(D, logits, k, **kw):
+    ids, vals, status = D.classify_topk_cuda(torch.from_numpy(logits).cuda(), k, **kw)
+    torch.cuda.synchronize()
+    return ids.cpu().numpy(), vals.cpu().numpy(), status.cpu().numpy()
+
+
+@pytest.mark.parametrize("name,seed,classes,k,rows", [("cls", 400, 1000, 5, 16), ("cls_small", 401, 10, 3, 4),
+                                                      ("cls_k1", 400, 1000, 1, 4)])
+def test_matches_reference_vectors(D, golden, name, seed, classes, k, rows):
+    logits = synth.logits(16 if name != "cls_small" else 4, seed=seed, classes=classes)[:rows]
+    ids, vals, status = _run(D, logits, k)
+    assert np.array_equal(ids, golden[f"{name}_ids"]) and not status.any()
+    np.testing.assert_allclose(vals.astype(np.float64), golden[f"{name}_probs"], rtol=RTOL, atol=0)
+
+
+@pytest.mark.parametrize("rows,classes,k", [(1, 1000, 5), (1035, 1000, 5), (7, 1, 1), (5, 33, 33), (3, 1001, 7),
+                                            (2, 21843, 5), (2, 40000, 3), (300, 100, 10)])
+def test_softmax_topk_vs_oracle(D, rows, classes, k):
+    logits = synth.logits(rows, seed=500 + classes, classes=classes)
+    ids, vals, status = _run(D, logits, k)
+    for r in range(rows):
+        want_ids, want_probs = O.softmax_topk(logits[r], k)
+        top = min(k, 5, classes)  # the generator separates the first five
+        assert ids[r, :top].tolist() == want_ids[:top].tolist()
+        np.testing.assert_allclose(vals[r, :top], want_probs[:top], rtol=RTOL, atol=0)
+        # beyond the separated five: same multiset of probabilities, order up to rounding
+        np.testing.assert_allclose(vals[r], want_probs, rtol=RTOL, atol=1e-30)
+        assert len(set(ids[r].tolist())) == k
+    assert not status.any()
+
+
+def test_argmax_raw_matches_np_argmax(D):
+    logits = synth.logits(64, seed=600)
+    logits[3, 10] = logits[3, 700] = 50.0  # tie: np.argmax takes the first
+    logits[4, 5] = np.nan  # np.argmax returns the first NaN
+    logits[4, 900] = np.nan
+    logits[5, :] = -0.0
+    logits[5, 17] = 0.0  # -0.0 == +0.0: still the first index
+    ids, vals, status = _run(D, logits, 1, softmax=False, low_index_first=True)
+    for r in range(64):
+        cid, conf = O.top1(logits[r][None])
+        assert ids[r, 0] == cid
+        assert vals[r, 0] == conf or (np.isnan(conf) and np.isnan(vals[r, 0]))
+    assert status[4] == 1 and status.sum() == 1
+
+
+def test_ties_and_special_values(D):
+    x = synth.logits(6, seed=601, classes=50)
+    x[0, 7] = x[0, 30] = 40.0  # equal probabilities: larger index first (stable sort reversed)
+    x[1, 11] = np.nan  # every probability NaN
+    x[2, 3] = np.inf  # inf - inf -> NaN in the sum -> every probability NaN
+    x[3, :] = -np.inf
+    x[4, :] = 3.0  # uniform
+    ids, vals, status = _run(D, x, 4)
+    assert ids[0, :2].tolist() == [30, 7] and vals[0, 0] == vals[0, 1]
+    for r in (1, 2, 3):
+        assert np.isnan(vals[r]).all() and ids[r].tolist() == [49, 48, 47, 46]
+    assert status.tolist() == [0, 1, 0, 0, 0, 0]
+    assert ids[4].tolist() == [49, 48, 47, 46]
+    np.testing.assert_allclose(vals[4], np.float32(1.0) / np.float32(50.0), rtol=1e-6)
+    want_ids, want_probs = O.softmax_topk(x[5], 4)
+    assert ids[5].tolist() == want_ids.tolist()
+
+
+def test_large_magnitudes_are_stable(D):
+    x = synth.logits(4, seed=602) * np.float32(50.0)  # exp() of the raw values would overflow
+    ids, vals, _ = _run(D, x, 5)
+    for r in range(4):
+        want_ids, want_probs = O.softmax_topk(x[r], 5)
+        assert ids[r].tolist() == want_ids.tolist()
+        np.testing.assert_allclose(vals[r], want_probs, rtol=RTOL, atol=1e-38)
+
+
+def test_argument_checks(D):
+    x = torch.zeros((2, 10), device="cuda")
+    with pytest.raises(RuntimeError, match="invalid"):
+        D.classify_topk_cuda(x, 11)
+    with pytest.raises(RuntimeError):
+        D.classify_topk_cuda(torch.zeros((1, 60000), device="cuda"), 1)
+    ids, vals, status = D.classify_topk_cuda(torch.zeros((0, 10), device="cuda"), 3)
+    assert ids.shape == (0, 3)
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        D.classify_topk_cuda(torch.zeros((2, 10)), 1)
+
+
+def test_numpy_wrappers(golden):
+    from shared.processing.classify import softmax_top_k, top1
+    row = synth.logits(16, seed=400)[2]
+    got = softmax_top_k(row, 5)
+    assert [g[0] for g in got] == golden["cls_ids"][2].tolist()
+    np.testing.assert_allclose([g[1] for g in got], golden["cls_probs"][2], rtol=RTOL)
+    assert top1(row[None]) == O.top1(row[None])
+    assert len(softmax_top_k(row[:3], 5)) == 3
+    with pytest.raises(ValueError):
+        softmax_top_k(np.zeros((2, 3)))

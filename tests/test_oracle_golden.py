@@ -82,6 +82,25 @@ def test_v8_parse(golden):
         assert np.array_equal(dets, golden[f"v8_{n}_dets"])
 
 
+CLASSIFIER_CASES = {"cls": (lambda: synth.logits(16, seed=400), 5),
+                    "cls_small": (lambda: synth.logits(4, seed=401, classes=10), 3),
+                    "cls_k1": (lambda: synth.logits(16, seed=400)[:4], 1)}
+
+
+@pytest.mark.parametrize("name", list(CLASSIFIER_CASES))
+def test_softmax_topk(golden, name):
+    """N4: the reference's classify() (run with a stubbed session) vs the oracle.  Indices
+    exact; probabilities to 1e-6 relative — numpy picks its float32 exp() by CPU feature, so
+    another host may differ from the committed vectors in the last bit."""
+    make, k = CLASSIFIER_CASES[name]
+    for r, row in enumerate(make()):
+        idx, probs = P.softmax_topk(row, k)
+        assert idx.tolist() == golden[f"{name}_ids"][r].tolist()
+        assert probs.dtype == np.float32
+        np.testing.assert_allclose(probs.astype(np.float64), golden[f"{name}_probs"][r], rtol=1e-6, atol=0)
+        assert P.top1(row[None]) == (int(np.argmax(row)), float(row.max()))
+
+
 def test_c1_chain(golden):
     frame = synth.frames(1, 480, 640, seed=0)[0]
     head = synth.head_v5(1, seed=1, objects=4)

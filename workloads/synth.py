@@ -114,3 +114,19 @@ def detections(n: int, seed: int, kmax: int = 8, size: float = 640.0):
         dets[i, :k, 4] = rng.uniform(0.25, 0.99, size=k).astype(np.float32)
         dets[i, :k, 5] = rng.integers(0, CLASSES, size=k).astype(np.float32)
     return dets, count
+
+
+def logits(rows: int, seed: int, classes: int = 1000, spread: float = 4.0) -> np.ndarray:
+    """MobileNetV2-like logits: N(0, spread) with, per row, the five largest values pushed at
+    least 0.05 apart so the top-5 order survives a 1-ulp difference in exp()."""
+    rng = np.random.default_rng(seed)
+    x = rng.normal(0.0, spread, (rows, classes)).astype(np.float32)
+    take = min(6, classes)
+    top = np.argsort(x, axis=1)[:, ::-1][:, :take]
+    for r in range(rows):
+        base = x[r, top[r, take - 1]]
+        for j in range(take - 1):
+            x[r, top[r, j]] = np.float32(base + 0.05 * (take - 1 - j) + abs(x[r, top[r, j]] - base))
+        order = np.argsort(x[r])[::-1][:take]
+        assert np.all(np.diff(x[r, order]) <= -0.04), "logit generator produced a near tie"
+    return x
