@@ -15,6 +15,10 @@
 // those are divided by the sum, and the order among them is settled by k warp-wide maxima of
 // a 64-bit key (ordered value bits : index).  Rows where that shortcut does not apply (NaN or
 // infinite logits, masses of equal values, k > 32) take k plain passes instead.
+//
+// Two kernels share that scheme: rows of up to 1024 classes (MobileNetV2: 1000) live in 32
+// registers per lane and never touch shared memory except for the candidate list; longer
+// rows are staged in shared memory.
 #include <math_constants.h>
 
 #include "ia_common.cuh"
@@ -190,6 +194,165 @@ __global__ void __launch_bounds__(kClassifyMaxWarps * 32) classify_topk_kernel(c
   if (lane == 0 && p.status) p.status[row] = has_nan ? 1 : 0;
 }
 
+// ---------------------------------------------------------------- rows of <= 1024 classes
+constexpr int kRegPerLane = 32;
+constexpr int kRegMaxClasses = kRegPerLane * 32;
+
+__device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
+
+template <bool kSoftmax, bool kVec>
+__global__ void __launch_bounds__(kClassifyMaxWarps * 32, 3) classify_topk_reg_kernel(const ClassifyParams p) {
+  __shared__ float cand_raw[kClassifyMaxWarps][kCandidates];  // e (softmax) or the raw value
+  __shared__ int cand_idx[kClassifyMaxWarps][kCandidates];
+  __shared__ int cand_count[kClassifyMaxWarps];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kClassifyMaxWarps + warp;
+  if (row >= p.rows) return;
+  const float* g = p.logits + (size_t)row * p.classes;
+  const int C = p.classes, k = p.k;
+  const uint32_t flip = p.low_index_first ? 0xffffffffu : 0u;
+  constexpr uint32_t kFull = 0xffffffffu;
+
+  // element j of this lane is class class_of(j); classes past the end read as -inf.  kVec
+  // (classes % 4 == 0, 16-byte aligned rows): 128-bit loads, four consecutive classes per lane
+  auto class_of = [lane](int j) { return kVec ? ((j >> 2) * 32 + lane) * 4 + (j & 3) : j * 32 + lane; };
+  float x[kRegPerLane];
+  if (kVec) {
+#pragma unroll
+    for (int q = 0; q < kRegPerLane / 4; ++q) {
+      const int i = (q * 32 + lane) * 4;
+      const float4 f = i < C ? __ldg(reinterpret_cast<const float4*>(g + i))
+                             : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+      x[4 * q] = f.x, x[4 * q + 1] = f.y, x[4 * q + 2] = f.z, x[4 * q + 3] = f.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < kRegPerLane; ++j) x[j] = class_of(j) < C ? __ldg(g + class_of(j)) : -CUDART_INF_F;
+  }
+
+  uint32_t u[kRegPerLane];  // ordered bits of what the selection compares (e or the raw value)
+  float total = 0.f;
+  bool slow = k > 32;
+  if (kSoftmax) {
+    float m = x[0];
+#pragma unroll
+    for (int j = 1; j < kRegPerLane; ++j) m = fmaxf(m, x[j]);  // a NaN is skipped here ...
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
+#pragma unroll
+    for (int j = 0; j < kRegPerLane; ++j) x[j] = expf(__fsub_rn(x[j], m));  // ... and surfaces here
+    float part[kRegPerLane];
+#pragma unroll
+    for (int j = 0; j < kRegPerLane; ++j) part[j] = x[j];
+#pragma unroll
+    for (int w = kRegPerLane / 2; w > 0; w >>= 1)
+#pragma unroll
+      for (int j = 0; j < w; ++j) part[j] = __fadd_rn(part[j], part[j + w]);
+    double acc = (double)part[0];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(kFull, acc, d);
+    total = (float)acc;
+    // every e is in [0, 1] unless a logit was NaN or the row maximum infinite; then the sum
+    // is NaN and so is every probability (numpy gives the same) -> plain passes
+    slow |= !(total == total);
+#pragma unroll
+    for (int j = 0; j < kRegPerLane; ++j) u[j] = __float_as_uint(x[j]);  // e >= 0: bits are ordered
+  } else {
+#pragma unroll
+    for (int j = 0; j < kRegPerLane; ++j) u[j] = class_of(j) < C ? order_bits(x[j]) : 0u;
+  }
+  uint32_t lane_max = u[0];
+#pragma unroll
+  for (int j = 1; j < kRegPerLane; ++j) lane_max = max(lane_max, u[j]);
+
+  bool has_nan = false;
+  if (!kSoftmax) has_nan = warp_max_u32(lane_max) == 0xffffffffu;  // NaN orders above everything
+
+  uint32_t bound = 0;
+  if (!slow) {
+    bool alive = true;
+    for (int j = 0; j < k; ++j) {
+      bound = warp_max_u32(alive ? lane_max : 0u);
+      const uint32_t owners = __ballot_sync(kFull, alive && lane_max == bound);
+      if (owners && lane == __ffs(owners) - 1) alive = false;
+    }
+    if (kSoftmax) {  // see classify_topk_kernel for the margin
+      const float e_bound = __uint_as_float(bound);
+      slow = !(e_bound >= 1e-30f);
+      bound = __float_as_uint(__fmul_rn(e_bound, 0.999999f));
+    }
+  }
+
+  int found = 0;
+  if (!slow) {
+    if (lane == 0) cand_count[warp] = 0;
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < kRegPerLane; ++j) {
+      if (u[j] >= bound) {  // padding holds 0 < bound
+        const int pos = atomicAdd(&cand_count[warp], 1);
+        if (pos < kCandidates) cand_raw[warp][pos] = x[j], cand_idx[warp][pos] = class_of(j);
+      }
+    }
+    __syncwarp();
+    found = cand_count[warp];
+    slow = found > kCandidates;
+  }
+
+  const size_t out = (size_t)row * k;
+  if (!slow) {
+    // lane L owns candidates L and L+32: value to report, then its 64-bit key
+    float v0 = 0.f, v1 = 0.f;
+    uint64_t c0 = 0ull, c1 = 0ull;
+    if (lane < found) {
+      v0 = kSoftmax ? __fdiv_rn(cand_raw[warp][lane], total) : cand_raw[warp][lane];
+      c0 = ((uint64_t)order_bits(v0) << 32) | ((uint32_t)cand_idx[warp][lane] ^ flip);
+    }
+    if (lane + 32 < found) {
+      v1 = kSoftmax ? __fdiv_rn(cand_raw[warp][lane + 32], total) : cand_raw[warp][lane + 32];
+      c1 = ((uint64_t)order_bits(v1) << 32) | ((uint32_t)cand_idx[warp][lane + 32] ^ flip);
+    }
+    uint64_t prev = ~0ull;
+    for (int j = 0; j < k; ++j) {
+      const uint64_t a = c0 < prev ? c0 : 0ull, b = c1 < prev ? c1 : 0ull;
+      const uint64_t mine = a > b ? a : b;
+      const uint32_t hi = warp_max_u32((uint32_t)(mine >> 32));
+      const uint32_t lo = warp_max_u32((uint32_t)(mine >> 32) == hi ? (uint32_t)mine : 0u);
+      prev = ((uint64_t)hi << 32) | lo;
+      if (mine == prev) {  // keys are unique: exactly one lane
+        p.ids[out + j] = (int)(lo ^ flip);
+        p.values[out + j] = mine == c0 ? v0 : v1;
+      }
+    }
+  } else {
+    if (kSoftmax) {
+#pragma unroll
+      for (int j = 0; j < kRegPerLane; ++j) {
+        x[j] = __fdiv_rn(x[j], total);
+        has_nan |= class_of(j) < C && isnan(__ldg(g + class_of(j)));
+      }
+      has_nan = __any_sync(kFull, has_nan);
+    }
+    uint64_t prev = ~0ull;
+    for (int r = 0; r < k; ++r) {
+      uint64_t best = 0;
+      float best_val = 0.f;
+#pragma unroll
+      for (int j = 0; j < kRegPerLane; ++j) {
+        const int i = class_of(j);
+        const uint64_t key = i < C ? (((uint64_t)order_bits(x[j]) << 32) | ((uint32_t)i ^ flip)) : 0ull;
+        if (key < prev && key > best) best = key, best_val = x[j];
+      }
+      prev = warp_max_u64(best);
+      if (best == prev) {
+        p.ids[out + r] = (int)((uint32_t)prev ^ flip);
+        p.values[out + r] = best_val;
+      }
+    }
+  }
+  if (lane == 0 && p.status) p.status[row] = has_nan ? 1 : 0;
+}
+
 }  // namespace ia
 
 extern "C" int ia_classify_topk(const float* logits_dev, int rows, int classes, int k, int softmax,
@@ -200,6 +363,22 @@ extern "C" int ia_classify_topk(const float* logits_dev, int rows, int classes, 
   IA_RETURN_IF(rows < 0 || classes < 1 || k < 1 || k > classes, IA_ERR_INVALID_ARGUMENT);
   if (rows == 0) return IA_OK;
   IA_RETURN_IF(!logits_dev || !ids_dev || !values_dev, IA_ERR_INVALID_ARGUMENT);
+  ClassifyParams p;
+  p.logits = logits_dev;
+  p.rows = rows, p.classes = classes, p.k = k;
+  p.softmax = softmax != 0, p.low_index_first = low_index_first != 0;
+  p.warps = kClassifyMaxWarps;
+  p.ids = ids_dev, p.values = values_dev, p.status = status_dev;
+  if (classes <= kRegMaxClasses) {
+    const int blocks = (rows + kClassifyMaxWarps - 1) / kClassifyMaxWarps;
+    const bool vec = (classes & 3) == 0 && ((uintptr_t)logits_dev & 15) == 0;
+    const dim3 grid(blocks), block(kClassifyMaxWarps * 32);
+    if (p.softmax && vec) classify_topk_reg_kernel<true, true><<<grid, block, 0, stream>>>(p);
+    else if (p.softmax) classify_topk_reg_kernel<true, false><<<grid, block, 0, stream>>>(p);
+    else if (vec) classify_topk_reg_kernel<false, true><<<grid, block, 0, stream>>>(p);
+    else classify_topk_reg_kernel<false, false><<<grid, block, 0, stream>>>(p);
+    return launch_status();
+  }
   const size_t row_bytes = (size_t)classes * sizeof(float);
   IA_RETURN_IF(row_bytes > kClassifySmemLimit, IA_ERR_UNSUPPORTED);
   int warps = (int)(kClassifySmemBudget / row_bytes);
@@ -220,12 +399,7 @@ extern "C" int ia_classify_topk(const float* logits_dev, int rows, int classes, 
       raised_for = dev;
     }
   }
-  ClassifyParams p;
-  p.logits = logits_dev;
-  p.rows = rows, p.classes = classes, p.k = k;
-  p.softmax = softmax != 0, p.low_index_first = low_index_first != 0;
   p.warps = warps;
-  p.ids = ids_dev, p.values = values_dev, p.status = status_dev;
   const int blocks = (rows + warps - 1) / warps;
   if (p.softmax) classify_topk_kernel<true><<<blocks, warps * 32, smem, stream>>>(p);
   else classify_topk_kernel<false><<<blocks, warps * 32, smem, stream>>>(p);

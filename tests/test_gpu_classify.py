@@ -36,7 +36,8 @@ def test_matches_reference_vectors(D, golden, name, seed, classes, k, rows):
 
 
 @pytest.mark.parametrize("rows,classes,k", [(1, 1000, 5), (1035, 1000, 5), (7, 1, 1), (5, 33, 33), (3, 1001, 7),
-                                            (2, 21843, 5), (2, 40000, 3), (300, 100, 10)])
+                                            (2, 21843, 5), (2, 40000, 3), (300, 100, 10), (4, 1024, 5),
+                                            (4, 1025, 5), (3, 64, 40), (9, 31, 6)])
 def test_softmax_topk_vs_oracle(D, rows, classes, k):
     logits = synth.logits(rows, seed=500 + classes, classes=classes)
     ids, vals, status = _run(D, logits, k)
@@ -49,6 +50,19 @@ def test_softmax_topk_vs_oracle(D, rows, classes, k):
         np.testing.assert_allclose(vals[r], want_probs, rtol=RTOL, atol=1e-30)
         assert len(set(ids[r].tolist())) == k
     assert not status.any()
+
+
+def test_unaligned_rows_take_the_scalar_loads(D):
+    logits = synth.logits(9, seed=640)
+    flat = torch.empty(logits.size + 1, dtype=torch.float32, device="cuda")
+    view = flat[1:].view(logits.shape)
+    view.copy_(torch.from_numpy(logits))
+    ids, vals, _ = D.classify_topk_cuda(view, 5)
+    ids2, vals2, _ = D.classify_topk_cuda(torch.from_numpy(logits).cuda(), 5)
+    # the two load patterns sum the row in different orders: last-bit differences allowed
+    assert torch.equal(ids, ids2) and torch.allclose(vals, vals2, rtol=1e-6, atol=0)
+    for r in range(9):
+        assert ids[r].tolist() == O.softmax_topk(logits[r], 5)[0].tolist()
 
 
 def test_argmax_raw_matches_np_argmax(D):
