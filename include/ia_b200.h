@@ -248,6 +248,71 @@ int ia_classify_topk(const float* logits_dev, int rows, int classes, int k, int 
                      int low_index_first, int32_t* ids_dev, float* values_dev,
                      int32_t* status_dev, void* stream);
 
+/* ---------------------------------------------------------------------------------
+ * JPEG decode on the device (the step before the path).  Replaces
+ * load_image_from_bytes, src/shared/processing/transforms.py:77-110 —
+ * cv2.imdecode(buf, IMREAD_COLOR) + cvtColor(BGR2RGB) — for baseline / extended-sequential
+ * Huffman JPEGs (8-bit; 1 component, or 3 components YCbCr in one interleaved scan;
+ * sampling 4:4:4, 4:2:2, 4:2:0, 4:4:0, 4:1:1; restart intervals; EXIF orientation).
+ * Bit-identical to libjpeg-turbo's default decoder as OpenCV drives it (islow IDCT, fancy
+ * upsampling, 16-bit fixed-point YCbCr->RGB), output directly in RGB.  Progressive,
+ * arithmetic-coded, 12-bit, CMYK and multi-scan files return IA_ERR_UNSUPPORTED from
+ * ia_jpeg_parse (they stay on the host decoder).  Only the compressed bytes cross PCIe.
+ *
+ *   1. ia_jpeg_parse       host: headers of one file -> ia_jpeg_job (no CUDA)
+ *   2. ia_jpeg_workspace_bytes / ia_jpeg_plan   host: carve the device workspace, fill the
+ *                          device pointers of every job
+ *   3. caller copies the file bytes and the job array to the device
+ *   4. ia_jpeg_decode      device: unstuff -> parallel Huffman -> IDCT -> upsample+colour
+ * ------------------------------------------------------------------------------- */
+#define IA_JPEG_MAX_COMPONENTS 3
+#define IA_JPEG_MAX_BLOCKS_PER_MCU 10
+
+typedef struct ia_jpeg_job {
+  /* --- filled by ia_jpeg_parse --- */
+  int32_t width, height;         /* as coded */
+  int32_t out_width, out_height; /* after the EXIF orientation (what imdecode returns) */
+  int32_t orientation;           /* EXIF tag 0x0112, 1..8 */
+  int32_t ncomp;
+  int32_t h[IA_JPEG_MAX_COMPONENTS], v[IA_JPEG_MAX_COMPONENTS]; /* sampling factors */
+  int32_t hmax, vmax;
+  int32_t mcux, mcuy, blocks_per_mcu, total_blocks;
+  int32_t restart_interval; /* MCUs, 0 = none */
+  int32_t num_segments;     /* restart segments = ceil(mcus / interval), 1 without */
+  uint32_t scan_offset;     /* first entropy-coded byte within the file */
+  uint32_t file_bytes;
+  uint8_t block_comp[IA_JPEG_MAX_BLOCKS_PER_MCU + 2]; /* component of block k of an MCU */
+  uint8_t block_bx[IA_JPEG_MAX_BLOCKS_PER_MCU + 2], block_by[IA_JPEG_MAX_BLOCKS_PER_MCU + 2];
+  uint8_t comp_dc[IA_JPEG_MAX_COMPONENTS + 1], comp_ac[IA_JPEG_MAX_COMPONENTS + 1]; /* table ids */
+  uint16_t quant[IA_JPEG_MAX_COMPONENTS][64]; /* natural order */
+  uint8_t dc_counts[4][16], dc_vals[4][16];
+  uint8_t ac_counts[4][16], ac_vals[4][256];
+  /* --- filled by ia_jpeg_plan (device pointers) --- */
+  const uint8_t* file_dev; /* the whole file */
+  uint8_t* clean_dev;      /* entropy-coded bytes without stuffing / RST markers */
+  uint32_t* segment_dev;   /* [num_segments + 1] info + restart boundaries (clean byte offsets) */
+  int16_t* coef_dev;       /* [total_blocks, 64] natural order, DC absolute, not dequantised */
+  uint8_t* plane_dev[IA_JPEG_MAX_COMPONENTS]; /* per component, padded to whole MCUs */
+  uint8_t* out_dev;        /* uint8 [out_height, out_width, 3] RGB */
+} ia_jpeg_job;
+
+/* sizeof(ia_jpeg_job) as the library was compiled, for bindings that mirror the struct. */
+size_t ia_jpeg_job_size(void);
+/* Host only.  IA_OK, IA_ERR_INVALID_ARGUMENT (not a JPEG / truncated headers: the reference
+ * raises "Failed to decode image from bytes") or IA_ERR_UNSUPPORTED. */
+int ia_jpeg_parse(const uint8_t* file_host, size_t file_bytes, ia_jpeg_job* job);
+/* Device scratch for n parsed jobs (clean streams, coefficients, planes). */
+size_t ia_jpeg_workspace_bytes(const ia_jpeg_job* jobs_host, int n);
+/* Host only: points job i at file_dev[i] / out_dev[i] and at its slices of the workspace
+ * (256-byte aligned base).  IA_ERR_WORKSPACE_TOO_SMALL if it does not fit. */
+int ia_jpeg_plan(ia_jpeg_job* jobs_host, int n, const uint8_t* const* file_dev,
+                 uint8_t* const* out_dev, void* workspace_dev, size_t workspace_bytes);
+/* jobs_dev: the planned job array copied to device memory by the caller (jobs_host is read
+ * for launch geometry only).  status_dev int32 [n]: 0 ok, bit 0 = the entropy-coded data
+ * ended early or overran (pixels then differ from libjpeg's error concealment). */
+int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* jobs_dev, int n,
+                   int32_t* status_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

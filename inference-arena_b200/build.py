@@ -19,7 +19,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "lib" / "libia_b200.so"
-SOURCES = ["ia_preprocess.cu", "ia_decode_nms.cu", "ia_crop.cu", "ia_float_crops.cu", "ia_classify.cu"]
+SOURCES = ["ia_preprocess.cu", "ia_decode_nms.cu", "ia_crop.cu", "ia_float_crops.cu", "ia_classify.cu", "ia_jpeg.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 

@@ -66,6 +66,11 @@ _SIGNATURES = {
                                         c_void_p]),
     "ia_imagenet_normalize_f32": (c_int, [c_void_p, c_size_t, F3, F3, c_void_p, c_void_p, c_size_t, c_void_p]),
     "ia_imagenet_normalize_u8": (c_int, [c_void_p, c_size_t, F3, F3, c_void_p, c_void_p]),
+    "ia_jpeg_job_size": (c_size_t, []),
+    "ia_jpeg_parse": (c_int, [c_void_p, c_size_t, c_void_p]),
+    "ia_jpeg_workspace_bytes": (c_size_t, [c_void_p, c_int]),
+    "ia_jpeg_plan": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t]),
+    "ia_jpeg_decode": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "ia_classify_topk": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                  c_void_p]),
 }

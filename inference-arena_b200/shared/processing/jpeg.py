@@ -1,0 +1,133 @@
+"""JPEG decode on the GPU: what ``load_image_from_bytes``
+(reference src/shared/processing/transforms.py:77-110) gets from ``cv2.imdecode`` +
+``cvtColor(BGR2RGB)``, for baseline / extended-sequential Huffman JPEGs, bit for bit.  Only the
+compressed bytes cross PCIe; frames are produced in HBM where K1 and K4 read them.
+
+Progressive, arithmetic-coded, 12-bit, CMYK and multi-scan files raise ``UnsupportedJpeg``;
+they (and PNG etc.) remain the business of the host-side ``transforms.load_image_from_bytes``.
+"""
+
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_int32, c_size_t, c_uint8, c_uint16, c_uint32, c_void_p
+
+import numpy as np
+import torch
+
+from . import _native
+from ._native import check, lib
+
+IA_ERR_UNSUPPORTED = -3
+
+
+class UnsupportedJpeg(ValueError):
+    """A valid JPEG of a flavour the device decoder does not take."""
+
+
+class JpegJob(ctypes.Structure):
+    """``ia_jpeg_job`` (include/ia_b200.h), field for field."""
+
+    _fields_ = [
+        ("width", c_int32), ("height", c_int32), ("out_width", c_int32), ("out_height", c_int32),
+        ("orientation", c_int32), ("ncomp", c_int32), ("h", c_int32 * 3), ("v", c_int32 * 3),
+        ("hmax", c_int32), ("vmax", c_int32), ("mcux", c_int32), ("mcuy", c_int32),
+        ("blocks_per_mcu", c_int32), ("total_blocks", c_int32), ("restart_interval", c_int32),
+        ("num_segments", c_int32), ("scan_offset", c_uint32), ("file_bytes", c_uint32),
+        ("block_comp", c_uint8 * 12), ("block_bx", c_uint8 * 12), ("block_by", c_uint8 * 12),
+        ("comp_dc", c_uint8 * 4), ("comp_ac", c_uint8 * 4), ("quant", (c_uint16 * 64) * 3),
+        ("dc_counts", (c_uint8 * 16) * 4), ("dc_vals", (c_uint8 * 16) * 4),
+        ("ac_counts", (c_uint8 * 16) * 4), ("ac_vals", (c_uint8 * 256) * 4),
+        ("file_dev", c_void_p), ("clean_dev", c_void_p), ("segment_dev", c_void_p), ("coef_dev", c_void_p),
+        ("plane_dev", c_void_p * 3), ("out_dev", c_void_p),
+    ]
+
+
+def _bind():
+    handle = lib()
+    if not hasattr(handle, "_jpeg_bound"):
+        handle.ia_jpeg_parse.argtypes = [c_void_p, c_size_t, ctypes.POINTER(JpegJob)]
+        handle.ia_jpeg_workspace_bytes.argtypes = [ctypes.POINTER(JpegJob), ctypes.c_int]
+        handle.ia_jpeg_plan.argtypes = [ctypes.POINTER(JpegJob), ctypes.c_int, ctypes.POINTER(c_void_p),
+                                        ctypes.POINTER(c_void_p), c_void_p, c_size_t]
+        handle.ia_jpeg_decode.argtypes = [ctypes.POINTER(JpegJob), c_void_p, ctypes.c_int, c_void_p, c_void_p]
+        if handle.ia_jpeg_job_size() != ctypes.sizeof(JpegJob):
+            raise RuntimeError("ia_jpeg_job layout mismatch between libia_b200.so and shared/processing/jpeg.py")
+        handle._jpeg_bound = True
+    return handle
+
+
+def parse_jpeg(image_bytes: bytes) -> JpegJob:
+    """Headers of one file (host only, no CUDA).  ``ValueError("Failed to decode ...")`` for
+    anything that is not a JPEG — the reference's message, transforms.py:100-106."""
+    if not image_bytes:
+        raise ValueError("Failed to decode image from bytes: empty input")
+    job = JpegJob()
+    rc = _bind().ia_jpeg_parse(ctypes.cast(ctypes.c_char_p(image_bytes), c_void_p), len(image_bytes),
+                               ctypes.byref(job))
+    if rc == IA_ERR_UNSUPPORTED:
+        raise UnsupportedJpeg("Failed to decode image from bytes: JPEG flavour not supported on the device "
+                              "(progressive / arithmetic / 12-bit / CMYK / multi-scan)")
+    if rc != 0:
+        raise ValueError("Failed to decode image from bytes")
+    return job
+
+
+class JpegBatch:
+    """Device buffers of one decoded batch (kept for inspection by tests and tools)."""
+
+    def __init__(self, jobs, frames, status, workspace, files_dev):
+        self.jobs, self.frames, self.status = jobs, frames, status
+        self.workspace, self.files_dev = workspace, files_dev
+
+    def coefficients(self, i: int) -> torch.Tensor:
+        """int16 [total_blocks, 64] of image i (natural order, DC absolute, not dequantised)."""
+        j = self.jobs[i]
+        off = j.coef_dev - self.workspace.data_ptr()
+        return self.workspace[off:off + j.total_blocks * 128].view(torch.int16).view(j.total_blocks, 64)
+
+
+def decode_jpeg_batch_cuda(blobs: list[bytes], device: torch.device | str | None = None) -> JpegBatch:
+    """Decode ``blobs`` (whole JPEG files) on ``device``; ``.frames[i]`` is uint8 [H, W, 3] RGB."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("decode_jpeg_batch_cuda needs a CUDA device (no CPU fallback in this path)")
+    handle = _bind()
+    dev = torch.device(device if device is not None else "cuda")
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    n = len(blobs)
+    jobs = (JpegJob * max(n, 1))()
+    for i, blob in enumerate(blobs):
+        jobs[i] = parse_jpeg(blob)
+    if n == 0:
+        return JpegBatch(jobs, [], torch.empty(0, dtype=torch.int32, device=dev), None, None)
+    offsets, total = [], 0
+    for blob in blobs:
+        offsets.append(total)
+        total += (len(blob) + 31) & ~15
+    staging = torch.empty(total, dtype=torch.uint8, pin_memory=True)
+    host = staging.numpy()
+    for off, blob in zip(offsets, blobs):
+        host[off:off + len(blob)] = np.frombuffer(blob, dtype=np.uint8)
+    with torch.cuda.device(dev):
+        files_dev = staging.to(dev, non_blocking=True)
+        frames = [torch.empty((jobs[i].out_height, jobs[i].out_width, 3), dtype=torch.uint8, device=dev)
+                  for i in range(n)]
+        need = handle.ia_jpeg_workspace_bytes(jobs, n)
+        workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+        file_ptrs = (c_void_p * n)(*[files_dev.data_ptr() + off for off in offsets])
+        out_ptrs = (c_void_p * n)(*[f.data_ptr() for f in frames])
+        check(handle.ia_jpeg_plan(jobs, n, file_ptrs, out_ptrs, workspace.data_ptr(), need), "ia_jpeg_plan")
+        jobs_host = torch.from_numpy(np.frombuffer(bytes(jobs), dtype=np.uint8)[: n * ctypes.sizeof(JpegJob)].copy())
+        jobs_dev = jobs_host.pin_memory().to(dev, non_blocking=True)
+        status = torch.empty(n, dtype=torch.int32, device=dev)
+        check(handle.ia_jpeg_decode(jobs, jobs_dev.data_ptr(), n, status.data_ptr(),
+                                    torch.cuda.current_stream(dev).cuda_stream), "ia_jpeg_decode")
+        jobs_dev.record_stream(torch.cuda.current_stream(dev))
+    return JpegBatch(jobs, frames, status, workspace, files_dev)
+
+
+def load_jpeg_from_bytes(image_bytes: bytes) -> np.ndarray:
+    """``load_image_from_bytes`` for a baseline JPEG, decoded on the GPU: RGB uint8 [H, W, 3]."""
+    batch = decode_jpeg_batch_cuda([image_bytes])
+    return batch.frames[0].cpu().numpy()

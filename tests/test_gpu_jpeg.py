@@ -1,0 +1,136 @@
+"""N3 parity: baseline JPEG decode on the GPU vs the oracle (oracle/jpeg.py, pinned against
+cv2.imdecode) and vs cv2.imdecode itself — the call load_image_from_bytes makes
+(transforms.py:102).  Pixels, coefficients and shapes: bit-exact."""
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import jpeg as J
+from workloads import jpeg_cases as W
+
+pytestmark = pytest.mark.gpu
+cv2 = pytest.importorskip("cv2")
+
+
+@pytest.fixture(scope="module")
+def M():
+    from shared.processing import jpeg
+    return jpeg
+
+
+def _scan_order_coefs(data):
+    """Oracle coefficients in the device layout: blocks in MCU scan order, natural order."""
+    info = J.parse(data)
+    coefs = J.decode_coefficients(data, info)
+    comps = info["comps"]
+    hmax, vmax = max(c["h"] for c in comps), max(c["v"] for c in comps)
+    mcux, mcuy = -(-info["width"] // (8 * hmax)), -(-info["height"] // (8 * vmax))
+    out = []
+    for my in range(mcuy):
+        for mx in range(mcux):
+            for c, cf in zip(comps, coefs):
+                for by in range(c["v"]):
+                    for bx in range(c["h"]):
+                        out.append(cf[my * c["v"] + by, mx * c["h"] + bx])
+    return np.stack(out)
+
+
+@pytest.mark.parametrize("sampling", W.SAMPLINGS)
+def test_coefficients_match_oracle(M, sampling):
+    data = W.encode(W.photo(40, 56, seed=21), 85, sampling)
+    batch = M.decode_jpeg_batch_cuda([data])
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0]
+    assert np.array_equal(batch.coefficients(0).cpu().numpy().astype(np.int64), _scan_order_coefs(data))
+
+
+@pytest.mark.parametrize("sampling", W.SAMPLINGS)
+@pytest.mark.parametrize("shape", [(16, 16), (48, 64), (33, 17), (17, 33), (1, 1), (2, 3), (8, 5), (5, 4), (64, 6)])
+def test_pixels_match_oracle(M, shape, sampling):
+    blobs, wants = [], []
+    for q, kw in ((5, {}), (50, {"restart": 3}), (90, {"optimize": True}), (100, {})):
+        data = W.encode(W.photo(*shape, seed=shape[0] * shape[1] + q), q, sampling, **kw)
+        blobs.append(data)
+        wants.append(J.load_image_from_bytes(data))
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0] * len(blobs)
+    for got, want in zip(batch.frames, wants):
+        assert got.shape == want.shape
+        assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_grayscale(M):
+    blobs = [W.encode(W.photo(*shape, seed=3)[..., 0], 80) for shape in ((20, 30), (7, 9), (31, 250))]
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    for got, data in zip(batch.frames, blobs):
+        assert np.array_equal(got.cpu().numpy(), W.reference_decode(data))
+
+
+@pytest.mark.parametrize("orientation", range(1, 9))
+def test_exif_orientation(M, orientation):
+    data = W.with_exif_orientation(W.encode(W.photo(24, 40, seed=9), 85, "420"), orientation)
+    got = M.load_jpeg_from_bytes(data)
+    want = W.reference_decode(data)
+    assert got.shape == want.shape and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("shape,sampling,q,restart", [
+    ((480, 640), "420", 90, 0), ((480, 640), "444", 75, 0), ((1080, 1920), "420", 90, 0),
+    ((1080, 1920), "422", 50, 120), ((1080, 1920), "420", 100, 0), ((721, 1283), "420", 95, 7),
+    ((300, 5000), "440", 80, 0)])
+def test_large_frames_match_cv2(M, shape, sampling, q, restart):
+    """Many 64 KB chunks, thousands of subsequences, the carried state between chunks."""
+    data = W.encode(W.photo(*shape, seed=shape[0] + q), q, sampling, restart=restart)
+    batch = M.decode_jpeg_batch_cuda([data])
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0]
+    assert np.array_equal(batch.frames[0].cpu().numpy(), W.reference_decode(data))
+
+
+def test_noise_image_long_codes(M):
+    """Pure noise at quality 100: long Huffman codes (slow-path look-ups), few end-of-blocks."""
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, (96, 128, 3), dtype=np.uint8)
+    for sampling in ("444", "420"):
+        data = W.encode(img, 100, sampling)
+        assert np.array_equal(M.load_jpeg_from_bytes(data), W.reference_decode(data))
+    flat = np.full((64, 64, 3), 77, np.uint8)  # DC-only blocks: almost no bits per block
+    data = W.encode(flat, 90, "420")
+    assert np.array_equal(M.load_jpeg_from_bytes(data), W.reference_decode(data))
+
+
+def test_mixed_batch(M):
+    """Different sizes, samplings and table sets in one call; two calls in a row."""
+    rng = np.random.default_rng(7)
+    blobs = []
+    for i in range(24):
+        h, w = int(rng.integers(1, 200)), int(rng.integers(1, 300))
+        img = W.photo(h, w, seed=100 + i)
+        if i % 5 == 4:
+            blobs.append(W.encode(img[..., 0], int(rng.integers(20, 100))))
+        else:
+            blobs.append(W.encode(img, int(rng.integers(20, 100)), W.SAMPLINGS[i % 5], restart=int(i % 3) * 2,
+                                  optimize=bool(i & 1)))
+    for _ in range(2):
+        batch = M.decode_jpeg_batch_cuda(blobs)
+        torch.cuda.synchronize()
+        assert batch.status.cpu().tolist() == [0] * len(blobs)
+        for got, data in zip(batch.frames, blobs):
+            assert np.array_equal(got.cpu().numpy(), W.reference_decode(data))
+
+
+def test_errors(M):
+    with pytest.raises(M.UnsupportedJpeg):
+        M.decode_jpeg_batch_cuda([W.encode(W.photo(16, 16, 1), 90, "420", progressive=True)])
+    with pytest.raises(ValueError, match="Failed to decode"):
+        M.load_jpeg_from_bytes(b"garbage")
+    assert M.decode_jpeg_batch_cuda([]).frames == []
+
+
+def test_truncated_stream_is_flagged(M):
+    data = W.encode(W.photo(64, 64, seed=2), 90, "420")
+    batch = M.decode_jpeg_batch_cuda([data[: len(data) * 2 // 3]])
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [1]
