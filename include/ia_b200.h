@@ -294,6 +294,9 @@ typedef struct ia_jpeg_job {
   int16_t* coef_dev;       /* [total_blocks, 64] natural order, DC absolute, not dequantised */
   uint8_t* plane_dev[IA_JPEG_MAX_COMPONENTS]; /* per component, padded to whole MCUs */
   uint8_t* out_dev;        /* uint8 [out_height, out_width, 3] RGB */
+  uint32_t* chain_dev;     /* per 64 KB chunk of the clean stream: hand-over record (zeroed per call) */
+  uint32_t* tile_dev;      /* per 8 KB tile of the scan: unstuffing counts */
+  uint32_t* ticket_dev;    /* one counter per call (shared by all jobs of the batch) */
 } ia_jpeg_job;
 
 /* sizeof(ia_jpeg_job) as the library was compiled, for bindings that mirror the struct. */

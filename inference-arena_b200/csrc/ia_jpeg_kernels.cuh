@@ -1,0 +1,716 @@
+// ia_jpeg_kernels.cuh — device side of the JPEG decoder (see ia_jpeg.cu for the overview).
+//
+//   U1 unstuff_count_kernel   per 8 KB tile of the entropy-coded bytes: how many bytes
+//                             survive (no FF00 stuffing, no RSTn markers), how many restart
+//                             markers, where the scan ends (first other marker)
+//   U2 unstuff_scan_kernel    per image: exclusive scan of the tile counts, totals
+//   U3 unstuff_scatter_kernel per tile: write the clean stream and the segment starts
+//   H  huffman_kernel         one CTA per 64 KB chunk of the clean stream (512 subsequences of
+//                             128 bytes, one per thread), self-synchronising decode inside
+//                             the CTA, chunks chained through a ticketed look-back
+//   I  idct_kernel            one thread per 8x8 block, jidctint.c "islow"
+//   C  colour_kernel          four pixels per thread: fancy upsampling, YCbCr->RGB, orientation
+#pragma once
+
+#include "ia_common.cuh"
+
+namespace ia {
+namespace jpeg {
+
+constexpr int kSubseqBytes = 128;
+constexpr int kSubseqBits = kSubseqBytes * 8;
+constexpr int kHuffThreads = 512;
+constexpr uint32_t kChunkBits = (uint32_t)kHuffThreads * kSubseqBits;
+constexpr uint32_t kChunkBytes = kChunkBits / 8;
+constexpr int kLutBits = 10;
+constexpr int kUnstuffThreads = 512;
+constexpr int kUnstuffPerThread = 16;
+constexpr uint32_t kTileBytes = kUnstuffThreads * kUnstuffPerThread;
+constexpr int kCleanPad = 64;   // readable zero bytes after the clean stream
+constexpr int kChainWords = 8;  // per chunk: flag, exit p, exit (b,z), blocks, dc0..2, pad
+constexpr int kTileWords = 4;   // per tile: kept bytes, markers, end position, pad
+
+__host__ __device__ inline uint32_t scan_bytes(const ia_jpeg_job& j) { return j.file_bytes - j.scan_offset; }
+__host__ __device__ inline uint32_t tile_capacity(const ia_jpeg_job& j) {
+  return (scan_bytes(j) + kTileBytes - 1) / kTileBytes + 1;
+}
+__host__ __device__ inline uint32_t chunk_capacity(const ia_jpeg_job& j) {
+  return (scan_bytes(j) + kChunkBytes - 1) / kChunkBytes + 1;
+}
+
+// ================================================================================ unstuff
+// Classify the 16 bytes [r0, r0+16) of the scan: which survive, which end a restart marker,
+// and the first position that starts any other marker (the end of the scan).
+__device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n, uint32_t r0, uint8_t (&b)[18],
+                                         uint32_t& keep_mask, uint32_t& bnd_mask, uint32_t& my_end) {
+#pragma unroll
+  for (int k = 0; k < kUnstuffPerThread + 2; ++k) {
+    const uint32_t idx = r0 + k - 1;  // b[k] = byte r0 - 1 + k; the byte before the scan reads as 0
+    b[k] = (r0 + k == 0) ? 0 : (idx < n ? __ldg(src + idx) : 0xD9);
+  }
+  keep_mask = 0, bnd_mask = 0, my_end = 0xffffffffu;
+#pragma unroll
+  for (int k = 0; k < kUnstuffPerThread; ++k) {
+    const uint32_t r = r0 + k;
+    const uint8_t prev = b[k], cur = b[k + 1], next = b[k + 2];
+    if (r < n) {
+      if (cur == 0xFF) {
+        if (next == 0x00) keep_mask |= 1u << k;
+        else if (next != 0xFF && !(next >= 0xD0 && next <= 0xD7)) my_end = min(my_end, r);
+      } else if (prev == 0xFF) {
+        if (cur >= 0xD0 && cur <= 0xD7) bnd_mask |= 1u << k;  // cur == 0 is stuffing: dropped
+      } else {
+        keep_mask |= 1u << k;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void cut_at(uint32_t end, uint32_t r0, uint32_t& keep_mask, uint32_t& bnd_mask) {
+  if (end < r0 + kUnstuffPerThread) {
+    const uint32_t valid = end > r0 ? end - r0 : 0;
+    const uint32_t m = (1u << valid) - 1u;  // valid < 16
+    keep_mask &= m, bnd_mask &= m;
+  }
+}
+
+// CTA-wide inclusive scan of a packed (markers << 16 | kept) count; returns the exclusive
+// value of this thread and, through `total`, the CTA total.
+__device__ __forceinline__ uint32_t cta_scan_packed(uint32_t mine, uint32_t* s_warp, uint32_t& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < kUnstuffThreads / 32 ? s_warp[lane] : 0;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, w, d);
+      if (lane >= d) w += o;
+    }
+    if (lane < kUnstuffThreads / 32) s_warp[lane] = w;
+  }
+  __syncthreads();
+  total = s_warp[kUnstuffThreads / 32 - 1];
+  return incl - mine + (warp ? s_warp[warp - 1] : 0);
+}
+
+__global__ void __launch_bounds__(kUnstuffThreads) unstuff_count_kernel(const ia_jpeg_job* __restrict__ jobs) {
+  const ia_jpeg_job& J = jobs[blockIdx.y];
+  const uint32_t n = scan_bytes(J);
+  const uint32_t tile = blockIdx.x;
+  if (tile >= tile_capacity(J)) return;
+  __shared__ uint32_t s_end, s_warp[kUnstuffThreads / 32];
+  if (threadIdx.x == 0) s_end = 0xffffffffu;
+  __syncthreads();
+  const uint32_t r0 = tile * kTileBytes + threadIdx.x * kUnstuffPerThread;
+  uint8_t b[18];
+  uint32_t keep_mask, bnd_mask, my_end;
+  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end);
+  if (my_end != 0xffffffffu) atomicMin(&s_end, my_end);
+  __syncthreads();
+  const uint32_t end = s_end;
+  cut_at(end, r0, keep_mask, bnd_mask);
+  uint32_t total;
+  cta_scan_packed((uint32_t)__popc(keep_mask) | ((uint32_t)__popc(bnd_mask) << 16), s_warp, total);
+  if (threadIdx.x == 0) {
+    uint32_t* t = J.tile_dev + (size_t)tile * kTileWords;
+    t[0] = total & 0xffffu, t[1] = total >> 16, t[2] = end;
+  }
+}
+
+// One warp per image walks the tiles: counts -> exclusive bases; tiles after the end of the
+// scan are marked dead (end = 0).  Also writes the totals and the zero padding.
+__global__ void __launch_bounds__(32) unstuff_scan_kernel(const ia_jpeg_job* __restrict__ jobs) {
+  const ia_jpeg_job& J = jobs[blockIdx.x];
+  const uint32_t tiles = tile_capacity(J);
+  const int lane = threadIdx.x;
+  uint32_t base_keep = 0, base_bnd = 0, scan_end = 0xffffffffu;
+  for (uint32_t t0 = 0; t0 < tiles; t0 += 32) {
+    const uint32_t t = t0 + lane;
+    uint32_t* rec = J.tile_dev + (size_t)t * kTileWords;
+    uint32_t keep = 0, bnd = 0, end = 0xffffffffu;
+    if (t < tiles) keep = rec[0], bnd = rec[1], end = rec[2];
+    // the first tile (in order) that saw an end marker closes the scan
+    const uint32_t ended = __ballot_sync(0xffffffffu, end != 0xffffffffu);
+    const int first = ended ? __ffs(ended) - 1 : 32;
+    const bool dead = scan_end != 0xffffffffu || lane > first;
+    if (dead) keep = 0, bnd = 0;
+    uint32_t ik = keep, ib = bnd;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t ok = __shfl_up_sync(0xffffffffu, ik, d), ob = __shfl_up_sync(0xffffffffu, ib, d);
+      if (lane >= d) ik += ok, ib += ob;
+    }
+    if (t < tiles) {
+      rec[0] = base_keep + ik - keep;
+      rec[1] = base_bnd + ib - bnd;
+      rec[2] = dead ? 0u : end;  // dead tiles keep nothing; live ones cut at their own end
+    }
+    base_keep += __shfl_sync(0xffffffffu, ik, 31);
+    base_bnd += __shfl_sync(0xffffffffu, ib, 31);
+    if (scan_end == 0xffffffffu && ended) scan_end = __shfl_sync(0xffffffffu, end, first);
+  }
+  for (int i = lane; i < kCleanPad; i += 32) J.clean_dev[base_keep + i] = 0;
+  if (lane == 0) {
+    J.segment_dev[0] = base_keep;
+    J.segment_dev[1] = min(base_bnd, (uint32_t)J.num_segments);
+  }
+}
+
+__global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const ia_jpeg_job* __restrict__ jobs) {
+  const ia_jpeg_job& J = jobs[blockIdx.y];
+  const uint32_t n = scan_bytes(J);
+  const uint32_t tile = blockIdx.x;
+  if (tile >= tile_capacity(J)) return;
+  const uint32_t* rec = J.tile_dev + (size_t)tile * kTileWords;
+  const uint32_t end = rec[2];
+  if (end == 0) return;  // after the end of the scan
+  __shared__ uint32_t s_warp[kUnstuffThreads / 32];
+  const uint32_t r0 = tile * kTileBytes + threadIdx.x * kUnstuffPerThread;
+  uint8_t b[18];
+  uint32_t keep_mask, bnd_mask, my_end;
+  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end);
+  cut_at(end, r0, keep_mask, bnd_mask);
+  uint32_t total;
+  const uint32_t excl = cta_scan_packed((uint32_t)__popc(keep_mask) | ((uint32_t)__popc(bnd_mask) << 16), s_warp, total);
+  uint32_t pos = rec[0] + (excl & 0xffffu);
+  uint32_t bpos = rec[1] + (excl >> 16);
+  uint8_t* __restrict__ clean = J.clean_dev;
+  uint32_t* __restrict__ seg = J.segment_dev;
+  const uint32_t seg_cap = (uint32_t)J.num_segments;
+#pragma unroll
+  for (int k = 0; k < kUnstuffPerThread; ++k) {
+    if (keep_mask >> k & 1u) clean[pos++] = b[k + 1];
+    if (bnd_mask >> k & 1u) {
+      if (bpos < seg_cap) seg[2 + bpos] = pos;  // the next segment starts at this clean byte
+      ++bpos;
+    }
+  }
+}
+
+// ================================================================================ Huffman
+struct HuffTables {
+  uint16_t lut[8][1 << kLutBits];  // (length << 8) | symbol for codes of <= kLutBits bits, else 0
+  int32_t maxcode[8][18];          // exclusive upper bound of the codes of each length, left-aligned to 16 bits
+  int32_t valoff[8][18];           // index of the first value of that length minus its first code
+  uint8_t vals[8][256];
+  uint8_t blk_comp[16], blk_dc[16], blk_ac[16];  // per block of an MCU: component, table rows
+  uint8_t natural[64];                           // zig-zag index -> natural (row-major) index
+};
+
+struct Agg {  // what a run of the stream contributes: completed blocks, DC sums, "predictors were reset"
+  int nb, flag, d0, d1, d2;
+};
+
+__device__ __forceinline__ Agg combine(const Agg& a, const Agg& b) {
+  Agg r;
+  r.nb = a.nb + b.nb;
+  if (b.flag) r.flag = 1, r.d0 = b.d0, r.d1 = b.d1, r.d2 = b.d2;
+  else r.flag = a.flag, r.d0 = a.d0 + b.d0, r.d1 = a.d1 + b.d1, r.d2 = a.d2 + b.d2;
+  return r;
+}
+
+__device__ __forceinline__ Agg shfl_up_agg(const Agg& a, int d) {
+  Agg r;
+  r.nb = __shfl_up_sync(0xffffffffu, a.nb, d);
+  r.flag = __shfl_up_sync(0xffffffffu, a.flag, d);
+  r.d0 = __shfl_up_sync(0xffffffffu, a.d0, d);
+  r.d1 = __shfl_up_sync(0xffffffffu, a.d1, d);
+  r.d2 = __shfl_up_sync(0xffffffffu, a.d2, d);
+  return r;
+}
+
+// symbol and code length for the code at the top of `bits`
+__device__ __forceinline__ void huff_lookup(const HuffTables& T, int t, uint32_t bits, int& sym, int& len) {
+  const uint32_t e = T.lut[t][bits >> (32 - kLutBits)];
+  if (e) {
+    sym = (int)(e & 255u), len = (int)(e >> 8);
+    return;
+  }
+  const int32_t code = (int32_t)(bits >> 16);
+  sym = 0, len = 16;  // an invalid code eats 16 bits and yields 0 (libjpeg warns and does the same)
+  for (int l = kLutBits + 1; l <= 16; ++l) {
+    if (code < T.maxcode[t][l]) {
+      sym = T.vals[t][(T.valoff[t][l] + (code >> (16 - l))) & 255];
+      len = l;
+      return;
+    }
+  }
+}
+
+__device__ __forceinline__ int extend(uint32_t v, int s) {  // T.81 F.2.2.1 EXTEND
+  return (int)v < (1 << (s - 1)) ? (int)v - (1 << s) + 1 : (int)v;
+}
+
+struct Stream {
+  const uint32_t* words;   // clean stream
+  uint32_t total_bits;
+  const uint32_t* bounds;  // restart boundaries (clean byte offsets), ascending
+  int num_bounds;
+  int bpm;
+};
+
+__device__ __forceinline__ uint32_t load_be(const uint32_t* __restrict__ words, uint32_t i) {
+  return __byte_perm(__ldg(words + i), 0, 0x0123);
+}
+
+// Decode from state (p, b, z) while p < end_bit.  kWrite: store coefficients of block `blk`
+// onwards with the DC predictors in agg.d*; otherwise only count (agg.d* accumulate the diffs).
+template <bool kWrite>
+__device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& T, uint32_t& p_io, int& b_io,
+                                             int& z_io, uint32_t end_bit, Agg& agg, int blk,
+                                             int16_t* __restrict__ coef, int total_blocks) {
+  uint32_t p = p_io;
+  int b = b_io, z = z_io;
+  // first boundary strictly after p; sitting exactly on one means "segment start"
+  int lo = 0, hi = S.num_bounds;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(S.bounds + mid) * 8u > p) hi = mid;
+    else lo = mid + 1;
+  }
+  int j = lo;
+  int dc[3] = {agg.d0, agg.d1, agg.d2};
+  if (j > 0 && __ldg(S.bounds + j - 1) * 8u == p) {
+    b = 0, z = 0, agg.flag = 1;
+    dc[0] = dc[1] = dc[2] = 0;
+  }
+  uint32_t next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
+  const uint32_t limit = min(end_bit, S.total_bits);
+
+  // 64-bit window whose top bit is stream bit p; at least 32 valid bits at the top of the loop
+  uint64_t window = 0;
+  uint32_t next_word = 0;
+  int avail = 0;
+  auto reload = [&]() {
+    const uint32_t i = p >> 5, off = p & 31u;
+    window = (((uint64_t)load_be(S.words, i) << 32) | load_be(S.words, i + 1)) << off;
+    avail = 64 - (int)off;
+    next_word = i + 2;
+  };
+  if (p < limit) reload();
+  while (p < limit) {
+    const uint32_t bits = (uint32_t)(window >> 32);
+    const int comp = T.blk_comp[b];
+    int sym, len;
+    huff_lookup(T, z == 0 ? T.blk_dc[b] : T.blk_ac[b], bits, sym, len);
+    const int s = sym & 15;  // DC: the category itself (<= 11 for 8-bit data); AC: low nibble
+    const uint32_t used = (uint32_t)(len + s);
+    if (p + used > S.total_bits) {  // the padding at the very end: nothing more to decode
+      p = S.total_bits;
+      break;
+    }
+    if (p + used > next_bound) {  // ran into the padding before a restart marker: new segment
+      p = next_bound, b = 0, z = 0, agg.flag = 1;
+      dc[0] = dc[1] = dc[2] = 0;
+      ++j;
+      next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
+      if (p < limit) reload();
+      continue;
+    }
+    const int value = s ? extend((bits << len) >> (32 - s), s) : 0;
+    p += used;
+    window <<= used;
+    avail -= (int)used;
+    if (avail < 32) {
+      window |= (uint64_t)load_be(S.words, next_word) << (32 - avail);
+      ++next_word;
+      avail += 32;
+    }
+    if (z == 0) {
+      dc[comp] += value;
+      if (kWrite && blk < total_blocks) coef[(size_t)blk * 64] = (int16_t)dc[comp];
+      z = 1;
+    } else if (s == 0) {
+      z = (sym >> 4) == 15 ? z + 16 : 64;
+    } else {
+      z += sym >> 4;
+      if (kWrite && z < 64 && blk < total_blocks) coef[(size_t)blk * 64 + T.natural[z]] = (int16_t)value;
+      ++z;
+    }
+    if (z >= 64) {
+      z = 0;
+      ++agg.nb;
+      if (kWrite) ++blk;
+      b = b + 1 == S.bpm ? 0 : b + 1;
+    }
+  }
+  if (p >= S.total_bits) p = S.total_bits, b = 0, z = 0;  // one canonical state past the end
+  agg.d0 = dc[0], agg.d1 = dc[1], agg.d2 = dc[2];
+  p_io = p, b_io = b, z_io = z;
+}
+
+__device__ __forceinline__ void build_tables(const ia_jpeg_job& J, HuffTables& T) {
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 8 * (1 << kLutBits); i += kHuffThreads) (&T.lut[0][0])[i] = 0;
+  for (int i = tid; i < 8 * 256; i += kHuffThreads) {
+    const int t = i >> 8, k = i & 255;
+    T.vals[t][k] = t < 4 ? (k < 16 ? J.dc_vals[t][k] : 0) : J.ac_vals[t - 4][k];
+  }
+  __syncthreads();
+  if (tid < 8) {
+    const uint8_t* counts = tid < 4 ? J.dc_counts[tid] : J.ac_counts[tid - 4];
+    int code = 0, k = 0;
+    for (int l = 1; l <= 16; ++l) {
+      const int cnt = counts[l - 1];
+      T.valoff[tid][l] = k - code;
+      for (int c = 0; c < cnt; ++c, ++k, ++code) {
+        if (l <= kLutBits) {
+          const uint16_t e = (uint16_t)((l << 8) | T.vals[tid][k & 255]);
+          const int first = code << (kLutBits - l);
+          for (int f = 0; f < (1 << (kLutBits - l)); ++f) T.lut[tid][(first + f) & ((1 << kLutBits) - 1)] = e;
+        }
+      }
+      // codes of this length are < maxcode (left-aligned to 16 bits); a length without codes
+      // inherits the previous bound so that it never matches
+      T.maxcode[tid][l] = cnt ? (code << (16 - l)) : (l > 1 ? T.maxcode[tid][l - 1] : 0);
+      code <<= 1;
+    }
+  } else if (tid >= 32 && tid < 48) {
+    const int i = tid - 32;
+    const int k = i < J.blocks_per_mcu ? i : 0;
+    const int c = J.block_comp[k];
+    T.blk_comp[i] = (uint8_t)c;
+    T.blk_dc[i] = J.comp_dc[c];
+    T.blk_ac[i] = (uint8_t)(4 + J.comp_ac[c]);
+  } else if (tid >= 64 && tid < 128) {
+    constexpr uint8_t kNatural[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,
+                                      12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6,  7,  14, 21, 28,
+                                      35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51,
+                                      58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+    T.natural[tid - 64] = kNatural[tid - 64];
+  }
+  __syncthreads();
+}
+
+// Chunks of one image are chained: a chunk needs the exact decoder state and the running
+// block count / DC predictors at its first bit, which only its predecessor knows.  Each CTA
+// first converges on guesses (no waiting), then takes a ticket-ordered look at the
+// predecessor's published record, repairs its first subsequences, publishes its own record and
+// only then writes coefficients.  Tickets are handed out in launch order, so the CTA a chunk
+// waits for is always already running.
+__global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job* __restrict__ jobs, int max_chunks,
+                                                               uint32_t* __restrict__ ticket_counter,
+                                                               int32_t* __restrict__ status) {
+  extern __shared__ __align__(16) unsigned char huff_smem[];
+  HuffTables& T = *reinterpret_cast<HuffTables*>(huff_smem);
+  __shared__ uint32_t s_exit_p[kHuffThreads], s_exit_bz[kHuffThreads];
+  __shared__ Agg s_warp_agg[kHuffThreads / 32];
+  __shared__ Agg s_carry;
+  __shared__ uint32_t s_in_p, s_in_bz, s_ticket;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_ticket = atomicAdd(ticket_counter, 1u);
+  __syncthreads();
+  const int image = (int)(s_ticket / (uint32_t)max_chunks), chunk = (int)(s_ticket % (uint32_t)max_chunks);
+  const ia_jpeg_job& J = jobs[image];
+
+  Stream S;
+  S.words = reinterpret_cast<const uint32_t*>(J.clean_dev);
+  S.total_bits = J.segment_dev[0] * 8u;
+  S.bounds = J.segment_dev + 2;
+  S.num_bounds = (int)J.segment_dev[1];
+  S.bpm = J.blocks_per_mcu;
+  const int num_chunks = S.total_bits ? (int)((S.total_bits + kChunkBits - 1) / kChunkBits) : 1;
+  if (chunk >= num_chunks) return;  // nothing waits on the spare CTAs of shorter images
+  build_tables(J, T);
+
+  const uint32_t begin = (uint32_t)chunk * kChunkBits + (uint32_t)tid * kSubseqBits, end = begin + kSubseqBits;
+  uint32_t ep = min(begin, S.total_bits), ebz = 0;  // entry state: a guess (exact for chunk 0, thread 0)
+  Agg agg;
+  auto run = [&]() {
+    uint32_t p = ep;
+    int b = (int)(ebz >> 8), z = (int)(ebz & 255u);
+    agg.nb = 0, agg.flag = 0, agg.d0 = agg.d1 = agg.d2 = 0;
+    decode_range<false>(S, T, p, b, z, end, agg, 0, nullptr, 0);
+    s_exit_p[tid] = p;
+    s_exit_bz[tid] = ((uint32_t)b << 8) | (uint32_t)z;
+  };
+  // repeat: whoever's predecessor ended in another state than assumed decodes again from it
+  auto converge = [&](bool first_known) {
+    for (;;) {
+      __syncthreads();
+      bool redo = false;
+      uint32_t np = 0, nbz = 0;
+      if (tid > 0) np = s_exit_p[tid - 1], nbz = s_exit_bz[tid - 1], redo = np != ep || nbz != ebz;
+      else if (first_known) np = s_in_p, nbz = s_in_bz, redo = np != ep || nbz != ebz;
+      if (!__syncthreads_or(redo)) break;  // also orders the reads above before the writes below
+      if (redo) {
+        ep = np, ebz = nbz;
+        run();
+      }
+    }
+  };
+  run();
+  converge(false);
+
+  if (tid == 0) {
+    if (chunk > 0) {
+      volatile uint32_t* rec = J.chain_dev + (size_t)(chunk - 1) * kChainWords;
+      while (rec[0] == 0) __nanosleep(64);
+      __threadfence();
+      s_in_p = rec[1], s_in_bz = rec[2];
+      s_carry.nb = (int)rec[3], s_carry.flag = 0;
+      s_carry.d0 = (int)rec[4], s_carry.d1 = (int)rec[5], s_carry.d2 = (int)rec[6];
+    } else {
+      s_in_p = 0, s_in_bz = 0;
+      s_carry.nb = 0, s_carry.flag = 0, s_carry.d0 = s_carry.d1 = s_carry.d2 = 0;
+    }
+  }
+  converge(true);  // its first barrier publishes s_in_* / s_carry
+
+  // ---- CTA scan of the contributions: output block and DC predictors at each thread's entry
+  Agg incl = agg;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const Agg o = shfl_up_agg(incl, d);
+    if (lane >= d) incl = combine(o, incl);
+  }
+  if (lane == 31) s_warp_agg[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    Agg w;
+    if (lane < kHuffThreads / 32) w = s_warp_agg[lane];
+    else w.nb = w.flag = w.d0 = w.d1 = w.d2 = 0;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const Agg o = shfl_up_agg(w, d);
+      if (lane >= d) w = combine(o, w);
+    }
+    if (lane < kHuffThreads / 32) s_warp_agg[lane] = w;
+  }
+  __syncthreads();
+  Agg before = s_carry;  // everything before this thread: carry (+) earlier warps (+) earlier lanes
+  if (warp > 0) before = combine(before, s_warp_agg[warp - 1]);
+  {
+    const Agg prev_lane = shfl_up_agg(incl, 1);
+    if (lane > 0) before = combine(before, prev_lane);
+  }
+  if (tid == 0) {  // publish before writing coefficients: the successor does not need them
+    const Agg out = combine(s_carry, s_warp_agg[kHuffThreads / 32 - 1]);
+    uint32_t* rec = J.chain_dev + (size_t)chunk * kChainWords;
+    rec[1] = s_exit_p[kHuffThreads - 1], rec[2] = s_exit_bz[kHuffThreads - 1];
+    rec[3] = (uint32_t)out.nb, rec[4] = (uint32_t)out.d0, rec[5] = (uint32_t)out.d1, rec[6] = (uint32_t)out.d2;
+    __threadfence();
+    *reinterpret_cast<volatile uint32_t*>(rec) = 1u;
+    if (chunk == num_chunks - 1) status[image] = out.nb == J.total_blocks ? 0 : 1;
+  }
+
+  // ---- write pass from the exact entry state
+  Agg w;
+  w.nb = 0, w.flag = 0, w.d0 = before.d0, w.d1 = before.d1, w.d2 = before.d2;
+  uint32_t p = ep;
+  int b = (int)(ebz >> 8), z = (int)(ebz & 255u);
+  decode_range<true>(S, T, p, b, z, end, w, before.nb, J.coef_dev, J.total_blocks);
+}
+
+// =================================================================================== IDCT
+constexpr int kIdctThreads = 128;
+
+#define IA_FIX_0_298631336 2446
+#define IA_FIX_0_390180644 3196
+#define IA_FIX_0_541196100 4433
+#define IA_FIX_0_765366865 6270
+#define IA_FIX_0_899976223 7373
+#define IA_FIX_1_175875602 9633
+#define IA_FIX_1_501321110 12299
+#define IA_FIX_1_847759065 15137
+#define IA_FIX_1_961570560 16069
+#define IA_FIX_2_053119869 16819
+#define IA_FIX_2_562915447 20995
+#define IA_FIX_3_072711026 25172
+
+// one 8-point pass of jidctint.c; outputs are not yet descaled
+__device__ __forceinline__ void idct8(const int d[8], int o[8]) {
+  int z1 = (d[2] + d[6]) * IA_FIX_0_541196100;
+  const int tmp2 = z1 + d[6] * (-IA_FIX_1_847759065);
+  const int tmp3 = z1 + d[2] * IA_FIX_0_765366865;
+  const int tmp0 = (d[0] + d[4]) << 13, tmp1 = (d[0] - d[4]) << 13;
+  const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+  int t0 = d[7], t1 = d[5], t2 = d[3], t3 = d[1];
+  z1 = t0 + t3;
+  int z2 = t1 + t2, z3 = t0 + t2, z4 = t1 + t3;
+  const int z5 = (z3 + z4) * IA_FIX_1_175875602;
+  t0 *= IA_FIX_0_298631336, t1 *= IA_FIX_2_053119869, t2 *= IA_FIX_3_072711026, t3 *= IA_FIX_1_501321110;
+  z1 *= -IA_FIX_0_899976223, z2 *= -IA_FIX_2_562915447, z3 *= -IA_FIX_1_961570560, z4 *= -IA_FIX_0_390180644;
+  z3 += z5, z4 += z5;
+  t0 += z1 + z3, t1 += z2 + z4, t2 += z2 + z3, t3 += z1 + z4;
+  o[0] = tmp10 + t3, o[7] = tmp10 - t3, o[1] = tmp11 + t2, o[6] = tmp11 - t2;
+  o[2] = tmp12 + t1, o[5] = tmp12 - t1, o[3] = tmp13 + t0, o[4] = tmp13 - t0;
+}
+
+// libjpeg's range_limit[x & RANGE_MASK] with the table centred on 128
+__device__ __forceinline__ uint32_t range_limit(int x) {
+  const int i = x & 1023;
+  return i < 128 ? i + 128 : (i < 512 ? 255 : (i < 896 ? 0 : i - 896));
+}
+
+__global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* __restrict__ jobs) {
+  const ia_jpeg_job& J = jobs[blockIdx.y];
+  __shared__ uint16_t s_quant[IA_JPEG_MAX_COMPONENTS][64];
+  for (int i = threadIdx.x; i < IA_JPEG_MAX_COMPONENTS * 64; i += kIdctThreads)
+    (&s_quant[0][0])[i] = (&J.quant[0][0])[i];
+  __syncthreads();
+  const int g = blockIdx.x * kIdctThreads + threadIdx.x;
+  if (g >= J.total_blocks) return;
+  const int bpm = J.blocks_per_mcu;
+  const int mcu = g / bpm, k = g - mcu * bpm;
+  const int my = mcu / J.mcux, mx = mcu - my * J.mcux;
+  const int c = J.block_comp[k];
+  const int bx = mx * J.h[c] + J.block_bx[k], by = my * J.v[c] + J.block_by[k];
+  const int pitch = J.mcux * J.h[c] * 8;
+  uint8_t* __restrict__ dst = J.plane_dev[c] + (size_t)by * 8 * pitch + (size_t)bx * 8;
+
+  const uint4* __restrict__ src = reinterpret_cast<const uint4*>(J.coef_dev + (size_t)g * 64);
+  const uint16_t* q = s_quant[c];
+  int ws[64];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const uint4 v = __ldg(src + r);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      ws[r * 8 + 2 * i] = (int)(int16_t)(w[i] & 0xffffu) * (int)q[r * 8 + 2 * i];
+      ws[r * 8 + 2 * i + 1] = (int)(int16_t)(w[i] >> 16) * (int)q[r * 8 + 2 * i + 1];
+    }
+  }
+  // pass 1: columns, descale by CONST_BITS - PASS1_BITS = 11
+#pragma unroll
+  for (int col = 0; col < 8; ++col) {
+    int d[8], o[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) d[r] = ws[r * 8 + col];
+    idct8(d, o);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) ws[r * 8 + col] = (o[r] + (1 << 10)) >> 11;
+  }
+  // pass 2: rows, descale by CONST_BITS + PASS1_BITS + 3 = 18, range-limit, store
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    int d[8], o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) d[i] = ws[r * 8 + i];
+    idct8(d, o);
+    uint32_t px[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) px[i] = range_limit((o[i] + (1 << 17)) >> 18);
+    uint2 out;
+    out.x = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
+    out.y = px[4] | (px[5] << 8) | (px[6] << 16) | (px[7] << 24);
+    *reinterpret_cast<uint2*>(dst + (size_t)r * pitch) = out;
+  }
+}
+
+// ====================================================================== upsample + colour
+__device__ __forceinline__ int chroma_sample(const uint8_t* __restrict__ plane, int pitch, int dw, int dh, int hexp,
+                                             int vexp, int x, int y) {
+  // jdsample.c: fancy upsampling for factors of two (h2v1 / h2v2 only when the subsampled
+  // width exceeds 2), plain replication otherwise
+  if (hexp == 1 && vexp == 1) return plane[(size_t)y * pitch + x];
+  if (hexp == 2 && vexp == 1 && dw > 2) {
+    const int xc = x >> 1;
+    const uint8_t* row = plane + (size_t)y * pitch;
+    const int a = row[xc];
+    if (x == 0 || x == 2 * dw - 1) return a;
+    return (x & 1) ? (3 * a + row[xc + 1] + 2) >> 2 : (3 * a + row[xc - 1] + 1) >> 2;
+  }
+  if (hexp == 2 && vexp == 2 && dw > 2) {
+    const int xc = x >> 1, yc = y >> 1;
+    int yo = (y & 1) ? yc + 1 : yc - 1;
+    yo = yo < 0 ? 0 : (yo > dh - 1 ? dh - 1 : yo);
+    const uint8_t* r0 = plane + (size_t)yc * pitch;
+    const uint8_t* r1 = plane + (size_t)yo * pitch;
+    const int cur = 3 * r0[xc] + r1[xc];
+    const int xo = (x & 1) ? xc + 1 : xc - 1;
+    const int bias = (x & 1) ? 7 : 8;
+    if (xo < 0 || xo > dw - 1) return (4 * cur + bias) >> 4;
+    return (3 * cur + 3 * r0[xo] + r1[xo] + bias) >> 4;
+  }
+  if (hexp == 1 && vexp == 2) {
+    const int yc = y >> 1;
+    int yo = (y & 1) ? yc + 1 : yc - 1;
+    yo = yo < 0 ? 0 : (yo > dh - 1 ? dh - 1 : yo);
+    return (3 * plane[(size_t)yc * pitch + x] + plane[(size_t)yo * pitch + x] + ((y & 1) ? 2 : 1)) >> 2;
+  }
+  return plane[(size_t)(y / vexp) * pitch + x / hexp];
+}
+
+constexpr int kColourPixels = 4;  // consecutive pixels of a row per thread
+
+__global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restrict__ jobs) {
+  const ia_jpeg_job& J = jobs[blockIdx.z];
+  const int x0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * kColourPixels, y = blockIdx.y * 8 + (threadIdx.x >> 5);
+  const int W = J.width, H = J.height;
+  if (x0 >= W || y >= H) return;
+  const int pitch_y = J.mcux * J.h[0] * 8;
+  const uint8_t* __restrict__ yrow = J.plane_dev[0] + (size_t)y * pitch_y;
+  const int ncomp = J.ncomp, orientation = J.orientation;
+  int hexp[2] = {1, 1}, vexp[2] = {1, 1}, dw[2] = {0, 0}, dh[2] = {0, 0}, pitch[2] = {0, 0};
+  if (ncomp == 3) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      hexp[k] = J.hmax / J.h[k + 1], vexp[k] = J.vmax / J.v[k + 1];
+      dw[k] = (W * J.h[k + 1] + J.hmax - 1) / J.hmax, dh[k] = (H * J.v[k + 1] + J.vmax - 1) / J.vmax;
+      pitch[k] = J.mcux * J.h[k + 1] * 8;
+    }
+  }
+  uint8_t rgb[kColourPixels * 3];
+  const int count = min(kColourPixels, W - x0);
+#pragma unroll
+  for (int i = 0; i < kColourPixels; ++i) {
+    const int x = min(x0 + i, W - 1);
+    const int yy = yrow[x];
+    int r, g, b;
+    if (ncomp == 1) {
+      r = g = b = yy;
+    } else {
+      const int cb = chroma_sample(J.plane_dev[1], pitch[0], dw[0], dh[0], hexp[0], vexp[0], x, y) - 128;
+      const int cr = chroma_sample(J.plane_dev[2], pitch[1], dw[1], dh[1], hexp[1], vexp[1], x, y) - 128;
+      // jdcolor.c build_ycc_rgb_table: FIX(1.40200)=91881, FIX(1.77200)=116130,
+      // FIX(0.71414)=46802, FIX(0.34414)=22554, ONE_HALF=32768, arithmetic shifts
+      r = yy + ((91881 * cr + 32768) >> 16);
+      g = yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16);
+      b = yy + ((116130 * cb + 32768) >> 16);
+      r = r < 0 ? 0 : (r > 255 ? 255 : r);
+      g = g < 0 ? 0 : (g > 255 ? 255 : g);
+      b = b < 0 ? 0 : (b > 255 ? 255 : b);
+    }
+    rgb[3 * i] = (uint8_t)r, rgb[3 * i + 1] = (uint8_t)g, rgb[3 * i + 2] = (uint8_t)b;
+  }
+  if (orientation == 1) {
+    uint8_t* o = J.out_dev + ((size_t)y * W + x0) * 3;
+    if (count == kColourPixels && ((uintptr_t)o & 3) == 0) {
+      uint32_t* o32 = reinterpret_cast<uint32_t*>(o);
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        o32[k] = rgb[4 * k] | (rgb[4 * k + 1] << 8) | (rgb[4 * k + 2] << 16) | ((uint32_t)rgb[4 * k + 3] << 24);
+    } else {
+      for (int k = 0; k < count * 3; ++k) o[k] = rgb[k];
+    }
+    return;
+  }
+  for (int i = 0; i < count; ++i) {  // OpenCV's ExifTransform
+    const int x = x0 + i;
+    int ox = x, oy = y;
+    switch (orientation) {
+      case 2: ox = W - 1 - x; break;
+      case 3: ox = W - 1 - x, oy = H - 1 - y; break;
+      case 4: oy = H - 1 - y; break;
+      case 5: ox = y, oy = x; break;
+      case 6: ox = H - 1 - y, oy = x; break;
+      case 7: ox = H - 1 - y, oy = W - 1 - x; break;
+      case 8: ox = y, oy = W - 1 - x; break;
+      default: break;
+    }
+    uint8_t* o = J.out_dev + ((size_t)oy * J.out_width + ox) * 3;
+    o[0] = rgb[3 * i], o[1] = rgb[3 * i + 1], o[2] = rgb[3 * i + 2];
+  }
+}
+
+}  // namespace jpeg
+}  // namespace ia

@@ -39,7 +39,8 @@ class JpegJob(ctypes.Structure):
         ("dc_counts", (c_uint8 * 16) * 4), ("dc_vals", (c_uint8 * 16) * 4),
         ("ac_counts", (c_uint8 * 16) * 4), ("ac_vals", (c_uint8 * 256) * 4),
         ("file_dev", c_void_p), ("clean_dev", c_void_p), ("segment_dev", c_void_p), ("coef_dev", c_void_p),
-        ("plane_dev", c_void_p * 3), ("out_dev", c_void_p),
+        ("plane_dev", c_void_p * 3), ("out_dev", c_void_p), ("chain_dev", c_void_p), ("tile_dev", c_void_p),
+        ("ticket_dev", c_void_p),
     ]
 
 
@@ -76,9 +77,15 @@ def parse_jpeg(image_bytes: bytes) -> JpegJob:
 class JpegBatch:
     """Device buffers of one decoded batch (kept for inspection by tests and tools)."""
 
-    def __init__(self, jobs, frames, status, workspace, files_dev):
+    def __init__(self, jobs, frames, status, workspace, files_dev, jobs_dev=None):
         self.jobs, self.frames, self.status = jobs, frames, status
-        self.workspace, self.files_dev = workspace, files_dev
+        self.workspace, self.files_dev, self.jobs_dev = workspace, files_dev, jobs_dev
+
+    def rerun(self) -> None:
+        """Launch the four decode kernels again on the resident compressed bytes (timing)."""
+        n = len(self.frames)
+        check(_bind().ia_jpeg_decode(self.jobs, self.jobs_dev.data_ptr(), n, self.status.data_ptr(),
+                                     torch.cuda.current_stream(self.status.device).cuda_stream), "ia_jpeg_decode")
 
     def coefficients(self, i: int) -> torch.Tensor:
         """int16 [total_blocks, 64] of image i (natural order, DC absolute, not dequantised)."""
@@ -124,7 +131,7 @@ def decode_jpeg_batch_cuda(blobs: list[bytes], device: torch.device | str | None
         check(handle.ia_jpeg_decode(jobs, jobs_dev.data_ptr(), n, status.data_ptr(),
                                     torch.cuda.current_stream(dev).cuda_stream), "ia_jpeg_decode")
         jobs_dev.record_stream(torch.cuda.current_stream(dev))
-    return JpegBatch(jobs, frames, status, workspace, files_dev)
+    return JpegBatch(jobs, frames, status, workspace, files_dev, jobs_dev)
 
 
 def load_jpeg_from_bytes(image_bytes: bytes) -> np.ndarray:
