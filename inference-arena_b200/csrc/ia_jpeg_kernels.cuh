@@ -27,7 +27,7 @@ constexpr int kUnstuffThreads = 512;
 constexpr int kUnstuffPerThread = 16;
 constexpr uint32_t kTileBytes = kUnstuffThreads * kUnstuffPerThread;
 constexpr int kCleanPad = 64;   // readable zero bytes after the clean stream
-constexpr int kChainWords = 8;  // per chunk: flag, exit p, exit (b,z), blocks, dc0..2, pad
+constexpr int kChainWords = 16;  // per chunk: tentative and final hand-over records (huffman_kernel)
 constexpr int kTileWords = 4;   // per tile: kept bytes, markers, end position, pad
 
 __host__ __device__ inline uint32_t scan_bytes(const ia_jpeg_job& j) { return j.file_bytes - j.scan_offset; }
@@ -400,7 +400,13 @@ __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job
                                                                int32_t* __restrict__ status) {
   extern __shared__ __align__(16) unsigned char huff_smem[];
   HuffTables& T = *reinterpret_cast<HuffTables*>(huff_smem);
+  // per subsequence: assumed entry state, resulting exit state and contribution
+  __shared__ uint32_t s_entry_p[kHuffThreads], s_entry_bz[kHuffThreads];
   __shared__ uint32_t s_exit_p[kHuffThreads], s_exit_bz[kHuffThreads];
+  __shared__ int s_nb[kHuffThreads], s_d0[kHuffThreads], s_d1[kHuffThreads], s_d2[kHuffThreads];
+  __shared__ uint8_t s_flag[kHuffThreads];
+  __shared__ uint16_t s_task[kHuffThreads];
+  __shared__ int s_wcount[kHuffThreads / 32];
   __shared__ Agg s_warp_agg[kHuffThreads / 32];
   __shared__ Agg s_carry;
   __shared__ uint32_t s_in_p, s_in_bz, s_ticket;
@@ -420,71 +426,136 @@ __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job
   if (chunk >= num_chunks) return;  // nothing waits on the spare CTAs of shorter images
   build_tables(J, T);
 
-  const uint32_t begin = (uint32_t)chunk * kChunkBits + (uint32_t)tid * kSubseqBits, end = begin + kSubseqBits;
-  uint32_t ep = min(begin, S.total_bits), ebz = 0;  // entry state: a guess (exact for chunk 0, thread 0)
-  Agg agg;
-  auto run = [&]() {
-    uint32_t p = ep;
-    int b = (int)(ebz >> 8), z = (int)(ebz & 255u);
-    agg.nb = 0, agg.flag = 0, agg.d0 = agg.d1 = agg.d2 = 0;
-    decode_range<false>(S, T, p, b, z, end, agg, 0, nullptr, 0);
-    s_exit_p[tid] = p;
-    s_exit_bz[tid] = ((uint32_t)b << 8) | (uint32_t)z;
+  const uint32_t chunk_begin = (uint32_t)chunk * kChunkBits;
+  // decode subsequence t from its assumed entry state; results go to shared memory
+  auto run = [&](int t) {
+    uint32_t p = s_entry_p[t];
+    const uint32_t bz = s_entry_bz[t];
+    int b = (int)(bz >> 8), z = (int)(bz & 255u);
+    Agg a;
+    a.nb = 0, a.flag = 0, a.d0 = a.d1 = a.d2 = 0;
+    decode_range<false>(S, T, p, b, z, chunk_begin + (uint32_t)(t + 1) * kSubseqBits, a, 0, nullptr, 0);
+    s_exit_p[t] = p;
+    s_exit_bz[t] = ((uint32_t)b << 8) | (uint32_t)z;
+    s_nb[t] = a.nb, s_d0[t] = a.d0, s_d1[t] = a.d1, s_d2[t] = a.d2;
+    s_flag[t] = (uint8_t)a.flag;
   };
-  // repeat: whoever's predecessor ended in another state than assumed decodes again from it
+  // Repeat: every subsequence whose predecessor ended in another state than assumed is decoded
+  // again from that state.  The repeats thin out quickly (hundreds, tens, a few ...), so they
+  // are compacted into a task list and run by the first threads of the CTA: a round with
+  // three tasks costs one warp, not sixteen.
+  int rounds = 0, tasks = 0;  // diagnostics, published with the chain record
   auto converge = [&](bool first_known) {
     for (;;) {
-      __syncthreads();
+      __syncthreads();  // exits of the previous round are visible
       bool redo = false;
       uint32_t np = 0, nbz = 0;
-      if (tid > 0) np = s_exit_p[tid - 1], nbz = s_exit_bz[tid - 1], redo = np != ep || nbz != ebz;
-      else if (first_known) np = s_in_p, nbz = s_in_bz, redo = np != ep || nbz != ebz;
-      if (!__syncthreads_or(redo)) break;  // also orders the reads above before the writes below
-      if (redo) {
-        ep = np, ebz = nbz;
-        run();
+      if (tid > 0) np = s_exit_p[tid - 1], nbz = s_exit_bz[tid - 1];
+      else if (first_known) np = s_in_p, nbz = s_in_bz;
+      if (tid > 0 || first_known) redo = np != s_entry_p[tid] || nbz != s_entry_bz[tid];
+      const uint32_t votes = __ballot_sync(0xffffffffu, redo);
+      if (lane == 0) s_wcount[warp] = __popc(votes);
+      __syncthreads();
+      int base = 0, total = 0;
+#pragma unroll
+      for (int w = 0; w < kHuffThreads / 32; ++w) {
+        const int c = s_wcount[w];
+        base += w < warp ? c : 0;
+        total += c;
       }
+      if (total == 0) break;
+      ++rounds, tasks += total;
+      if (redo) {
+        s_entry_p[tid] = np, s_entry_bz[tid] = nbz;
+        s_task[base + __popc(votes & ((1u << lane) - 1u))] = (uint16_t)tid;
+      }
+      __syncthreads();
+      if (tid < total) run(s_task[tid]);
     }
   };
-  run();
+  s_entry_p[tid] = min(chunk_begin + (uint32_t)tid * kSubseqBits, S.total_bits);  // a guess (exact for
+  s_entry_bz[tid] = 0;                                                             // chunk 0, thread 0)
+  run(tid);
   converge(false);
 
+  // Hand-over between the chunks of one image.  Record of a chunk (kChainWords words):
+  //   [0] tentative flag, [1..2] exit state after converging on guesses — right with near
+  //       certainty (the last subsequence is 64 KB downstream of the guess), so the successor
+  //       repairs its head from it at once, without waiting for this chunk's own repair;
+  //   [3] final flag, [4..5] exit state after the repair, [6..9] blocks and DC predictors up
+  //       to the end of this chunk, [10] diagnostics.
+  // The final records form the only serial chain, and a link of it is a compare and five adds.
+  uint32_t* my_rec = J.chain_dev + (size_t)chunk * kChainWords;
+  const volatile uint32_t* prev_rec = J.chain_dev + (size_t)(chunk > 0 ? chunk - 1 : 0) * kChainWords;
+  __shared__ int s_used_final, s_mismatch;
   if (tid == 0) {
-    if (chunk > 0) {
-      volatile uint32_t* rec = J.chain_dev + (size_t)(chunk - 1) * kChainWords;
-      while (rec[0] == 0) __nanosleep(64);
-      __threadfence();
-      s_in_p = rec[1], s_in_bz = rec[2];
-      s_carry.nb = (int)rec[3], s_carry.flag = 0;
-      s_carry.d0 = (int)rec[4], s_carry.d1 = (int)rec[5], s_carry.d2 = (int)rec[6];
+    my_rec[1] = s_exit_p[kHuffThreads - 1], my_rec[2] = s_exit_bz[kHuffThreads - 1];
+    __threadfence();
+    *reinterpret_cast<volatile uint32_t*>(my_rec) = 1u;
+    if (chunk == 0) {
+      s_in_p = 0, s_in_bz = 0, s_used_final = 1;
     } else {
-      s_in_p = 0, s_in_bz = 0;
-      s_carry.nb = 0, s_carry.flag = 0, s_carry.d0 = s_carry.d1 = s_carry.d2 = 0;
+      for (;;) {
+        if (prev_rec[3]) {
+          __threadfence();
+          s_in_p = prev_rec[4], s_in_bz = prev_rec[5], s_used_final = 1;
+          break;
+        }
+        if (prev_rec[0]) {
+          __threadfence();
+          s_in_p = prev_rec[1], s_in_bz = prev_rec[2], s_used_final = 0;
+          break;
+        }
+        __nanosleep(32);
+      }
     }
   }
-  converge(true);  // its first barrier publishes s_in_* / s_carry
+  converge(true);  // its first barrier publishes s_in_*
 
-  // ---- CTA scan of the contributions: output block and DC predictors at each thread's entry
-  Agg incl = agg;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const Agg o = shfl_up_agg(incl, d);
-    if (lane >= d) incl = combine(o, incl);
-  }
-  if (lane == 31) s_warp_agg[warp] = incl;
-  __syncthreads();
-  if (warp == 0) {
-    Agg w;
-    if (lane < kHuffThreads / 32) w = s_warp_agg[lane];
-    else w.nb = w.flag = w.d0 = w.d1 = w.d2 = 0;
+  // CTA scan of the contributions (without the carry): per-thread inclusive value, warp totals
+  Agg incl;
+  auto local_scan = [&]() {
+    incl.nb = s_nb[tid], incl.flag = s_flag[tid], incl.d0 = s_d0[tid], incl.d1 = s_d1[tid], incl.d2 = s_d2[tid];
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const Agg o = shfl_up_agg(w, d);
-      if (lane >= d) w = combine(o, w);
+      const Agg o = shfl_up_agg(incl, d);
+      if (lane >= d) incl = combine(o, incl);
     }
-    if (lane < kHuffThreads / 32) s_warp_agg[lane] = w;
+    if (lane == 31) s_warp_agg[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      Agg w;
+      if (lane < kHuffThreads / 32) w = s_warp_agg[lane];
+      else w.nb = w.flag = w.d0 = w.d1 = w.d2 = 0;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const Agg o = shfl_up_agg(w, d);
+        if (lane >= d) w = combine(o, w);
+      }
+      if (lane < kHuffThreads / 32) s_warp_agg[lane] = w;
+    }
+    __syncthreads();
+  };
+  local_scan();
+
+  // the predecessor's final record: running totals, and a check of the state this chunk assumed
+  if (tid == 0) {
+    s_mismatch = 0;
+    s_carry.nb = 0, s_carry.flag = 0, s_carry.d0 = s_carry.d1 = s_carry.d2 = 0;
+    if (chunk > 0) {
+      while (prev_rec[3] == 0) __nanosleep(32);
+      __threadfence();
+      const uint32_t fp = prev_rec[4], fbz = prev_rec[5];
+      s_carry.nb = (int)prev_rec[6];
+      s_carry.d0 = (int)prev_rec[7], s_carry.d1 = (int)prev_rec[8], s_carry.d2 = (int)prev_rec[9];
+      if (!s_used_final && (fp != s_in_p || fbz != s_in_bz)) s_in_p = fp, s_in_bz = fbz, s_mismatch = 1;
+    }
   }
   __syncthreads();
+  if (s_mismatch) {  // the tentative state was wrong after all (uniform branch): repair again
+    converge(true);
+    local_scan();
+  }
   Agg before = s_carry;  // everything before this thread: carry (+) earlier warps (+) earlier lanes
   if (warp > 0) before = combine(before, s_warp_agg[warp - 1]);
   {
@@ -493,20 +564,22 @@ __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job
   }
   if (tid == 0) {  // publish before writing coefficients: the successor does not need them
     const Agg out = combine(s_carry, s_warp_agg[kHuffThreads / 32 - 1]);
-    uint32_t* rec = J.chain_dev + (size_t)chunk * kChainWords;
-    rec[1] = s_exit_p[kHuffThreads - 1], rec[2] = s_exit_bz[kHuffThreads - 1];
-    rec[3] = (uint32_t)out.nb, rec[4] = (uint32_t)out.d0, rec[5] = (uint32_t)out.d1, rec[6] = (uint32_t)out.d2;
+    my_rec[4] = s_exit_p[kHuffThreads - 1], my_rec[5] = s_exit_bz[kHuffThreads - 1];
+    my_rec[6] = (uint32_t)out.nb, my_rec[7] = (uint32_t)out.d0, my_rec[8] = (uint32_t)out.d1;
+    my_rec[9] = (uint32_t)out.d2;
+    my_rec[10] = (uint32_t)rounds | ((uint32_t)min(tasks, 0xffff) << 16);
     __threadfence();
-    *reinterpret_cast<volatile uint32_t*>(rec) = 1u;
+    *reinterpret_cast<volatile uint32_t*>(my_rec + 3) = 1u;
     if (chunk == num_chunks - 1) status[image] = out.nb == J.total_blocks ? 0 : 1;
   }
 
   // ---- write pass from the exact entry state
   Agg w;
   w.nb = 0, w.flag = 0, w.d0 = before.d0, w.d1 = before.d1, w.d2 = before.d2;
-  uint32_t p = ep;
-  int b = (int)(ebz >> 8), z = (int)(ebz & 255u);
-  decode_range<true>(S, T, p, b, z, end, w, before.nb, J.coef_dev, J.total_blocks);
+  uint32_t p = s_entry_p[tid];
+  int b = (int)(s_entry_bz[tid] >> 8), z = (int)(s_entry_bz[tid] & 255u);
+  decode_range<true>(S, T, p, b, z, chunk_begin + (uint32_t)(tid + 1) * kSubseqBits, w, before.nb, J.coef_dev,
+                     J.total_blocks);
 }
 
 // =================================================================================== IDCT

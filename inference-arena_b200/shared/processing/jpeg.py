@@ -81,6 +81,13 @@ class JpegBatch:
         self.jobs, self.frames, self.status = jobs, frames, status
         self.workspace, self.files_dev, self.jobs_dev = workspace, files_dev, jobs_dev
 
+    def chain_records(self, i: int) -> torch.Tensor:
+        """int32 [chunks, 16] hand-over records of image i (word 10: repeat rounds | tasks << 16)."""
+        j = self.jobs[i]
+        off = j.chain_dev - self.workspace.data_ptr()
+        chunks = (j.file_bytes - j.scan_offset + 65535) // 65536 + 1
+        return self.workspace[off:off + chunks * 64].view(torch.int32).view(chunks, 16)
+
     def rerun(self) -> None:
         """Launch the four decode kernels again on the resident compressed bytes (timing)."""
         n = len(self.frames)

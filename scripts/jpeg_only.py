@@ -33,3 +33,6 @@ for b in blobs[:8]: cv2.cvtColor(cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IM
 cpu_ms = (time.perf_counter() - t0) / 8 * 1e3
 print(f"{batch_n} x {w}x{h} q{q} ({kb:.0f} KB/file): kernels {ms:.3f} ms -> {batch_n/ms*1e3:.0f} img/s; "
       f"whole call {call_ms:.1f} ms -> {batch_n/call_ms*1e3:.0f} img/s; cv2 one core {cpu_ms:.2f} ms/img")
+rec = batch.chain_records(0).cpu().numpy()
+live = rec[rec[:, 3] == 1]
+print("chunks", len(live), "rounds", (live[:, 10] & 0xffff).tolist(), "tasks", ((live[:, 10] >> 16) & 0xffff).tolist())
