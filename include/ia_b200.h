@@ -276,6 +276,10 @@ typedef struct ia_jpeg_job {
   int32_t ncomp;
   int32_t h[IA_JPEG_MAX_COMPONENTS], v[IA_JPEG_MAX_COMPONENTS]; /* sampling factors */
   int32_t hmax, vmax;
+  /* per component: real (subsampled) size, row pitch of its plane, upsampling factors */
+  int32_t comp_w[IA_JPEG_MAX_COMPONENTS], comp_h[IA_JPEG_MAX_COMPONENTS];
+  int32_t comp_pitch[IA_JPEG_MAX_COMPONENTS];
+  int32_t hexp[IA_JPEG_MAX_COMPONENTS], vexp[IA_JPEG_MAX_COMPONENTS];
   int32_t mcux, mcuy, blocks_per_mcu, total_blocks;
   int32_t restart_interval; /* MCUs, 0 = none */
   int32_t num_segments;     /* restart segments = ceil(mcus / interval), 1 without */

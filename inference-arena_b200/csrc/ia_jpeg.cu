@@ -186,6 +186,13 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
   job->blocks_per_mcu = bpm;
   job->mcux = (job->width + 8 * job->hmax - 1) / (8 * job->hmax);
   job->mcuy = (job->height + 8 * job->vmax - 1) / (8 * job->vmax);
+  for (int c = 0; c < job->ncomp; ++c) {
+    job->hexp[c] = job->hmax / job->h[c];
+    job->vexp[c] = job->vmax / job->v[c];
+    job->comp_w[c] = (job->width * job->h[c] + job->hmax - 1) / job->hmax;
+    job->comp_h[c] = (job->height * job->v[c] + job->vmax - 1) / job->vmax;
+    job->comp_pitch[c] = job->mcux * job->h[c] * 8;
+  }
   const long long mcus = (long long)job->mcux * job->mcuy;
   IA_RETURN_IF(mcus * bpm > 0x3fffffffLL, IA_ERR_UNSUPPORTED);
   job->total_blocks = (int32_t)(mcus * bpm);
@@ -317,8 +324,7 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
   unstuff_scatter_kernel<<<dim3(max_tiles, n), kUnstuffThreads, 0, stream>>>(jobs_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
-  static_assert(sizeof(HuffTables) + 8 * 1024 <= 48 * 1024, "huffman_kernel shared memory");
-  huffman_kernel<<<max_chunks * (unsigned)n, kHuffThreads, sizeof(HuffTables), stream>>>(
+  huffman_kernel<<<max_chunks * (unsigned)n, kHuffThreads, 0, stream>>>(
       jobs_dev, (int)max_chunks, jobs_host[0].ticket_dev, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;

@@ -195,14 +195,29 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
 }
 
 // ================================================================================ Huffman
+constexpr int kHuffSlots = 6;  // look-ups a scan can need: one DC and one AC per component
+
+// Packed look-up entry, one byte per field so that each is one PRMT/LOP away:
+//   byte 0  bits the symbol occupies (code length + magnitude bits, <= 31)
+//   byte 1  code length
+//   byte 2  32 - magnitude bits (the right shift that extracts them)
+//   byte 3  how far the zig-zag index moves: 1 for a DC symbol, run + 1 for a coefficient,
+//           16 for ZRL, 64 for end-of-block (anything that reaches 64 ends the block)
+// 0 = the code is longer than the look-up covers (huff_slow builds the entry on the fly).
 struct HuffTables {
-  uint16_t lut[8][1 << kLutBits];  // (length << 8) | symbol for codes of <= kLutBits bits, else 0
-  int32_t maxcode[8][18];          // exclusive upper bound of the codes of each length, left-aligned to 16 bits
-  int32_t valoff[8][18];           // index of the first value of that length minus its first code
-  uint8_t vals[8][256];
-  uint8_t blk_comp[16], blk_dc[16], blk_ac[16];  // per block of an MCU: component, table rows
-  uint8_t natural[64];                           // zig-zag index -> natural (row-major) index
+  uint32_t lut[kHuffSlots][1 << kLutBits];
+  int32_t maxcode[kHuffSlots][18];  // exclusive upper bound of the codes of each length, left-aligned to 16 bits
+  int32_t valoff[kHuffSlots][18];   // index of the first value of that length minus its first code
+  uint8_t vals[kHuffSlots][256];
+  uint32_t blk_info[16];  // per block of an MCU: component | DC slot << 8 | AC slot << 16
+  uint8_t natural[64];    // zig-zag index -> natural (row-major) index
 };
+
+__device__ __forceinline__ uint32_t pack_entry(int slot, int len, int sym) {
+  const int s = sym & 15, r = sym >> 4;
+  const int zinc = slot < 3 ? 1 : (s ? r + 1 : (r == 15 ? 16 : 64));
+  return (uint32_t)(len + s) | ((uint32_t)len << 8) | ((uint32_t)(32 - s) << 16) | ((uint32_t)zinc << 24);
+}
 
 struct Agg {  // what a run of the stream contributes: completed blocks, DC sums, "predictors were reset"
   int nb, flag, d0, d1, d2;
@@ -226,26 +241,13 @@ __device__ __forceinline__ Agg shfl_up_agg(const Agg& a, int d) {
   return r;
 }
 
-// symbol and code length for the code at the top of `bits`
-__device__ __forceinline__ void huff_lookup(const HuffTables& T, int t, uint32_t bits, int& sym, int& len) {
-  const uint32_t e = T.lut[t][bits >> (32 - kLutBits)];
-  if (e) {
-    sym = (int)(e & 255u), len = (int)(e >> 8);
-    return;
-  }
+// entry for a code longer than the look-up covers
+__device__ __noinline__ uint32_t huff_slow(const HuffTables& T, int slot, uint32_t bits) {
   const int32_t code = (int32_t)(bits >> 16);
-  sym = 0, len = 16;  // an invalid code eats 16 bits and yields 0 (libjpeg warns and does the same)
   for (int l = kLutBits + 1; l <= 16; ++l) {
-    if (code < T.maxcode[t][l]) {
-      sym = T.vals[t][(T.valoff[t][l] + (code >> (16 - l))) & 255];
-      len = l;
-      return;
-    }
+    if (code < T.maxcode[slot][l]) return pack_entry(slot, l, T.vals[slot][(T.valoff[slot][l] + (code >> (16 - l))) & 255]);
   }
-}
-
-__device__ __forceinline__ int extend(uint32_t v, int s) {  // T.81 F.2.2.1 EXTEND
-  return (int)v < (1 << (s - 1)) ? (int)v - (1 << s) + 1 : (int)v;
+  return pack_entry(slot, 16, 0);  // an invalid code eats 16 bits and yields 0 (libjpeg warns and does the same)
 }
 
 struct Stream {
@@ -276,109 +278,123 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
     else lo = mid + 1;
   }
   int j = lo;
-  int dc[3] = {agg.d0, agg.d1, agg.d2};
+  int dc0 = agg.d0, dc1 = agg.d1, dc2 = agg.d2;
   if (j > 0 && __ldg(S.bounds + j - 1) * 8u == p) {
     b = 0, z = 0, agg.flag = 1;
-    dc[0] = dc[1] = dc[2] = 0;
+    dc0 = dc1 = dc2 = 0;
   }
   uint32_t next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
   const uint32_t limit = min(end_bit, S.total_bits);
+  uint32_t stop = min(S.total_bits, next_bound);  // no symbol may cross this bit
+  uint32_t info = T.blk_info[b];                  // component | DC slot << 8 | AC slot << 16
+  int16_t* blk_ptr = kWrite ? coef + (size_t)blk * 64 : nullptr;
+  int nb = 0;
 
-  // 64-bit window whose top bit is stream bit p; at least 32 valid bits at the top of the loop
-  uint64_t window = 0;
-  uint32_t next_word = 0;
-  int avail = 0;
+  // three big-endian words of the stream: (w0:w1) holds bit p, w2 is fetched ahead
+  uint32_t w0 = 0, w1 = 0, w2 = 0, widx = 0;
   auto reload = [&]() {
-    const uint32_t i = p >> 5, off = p & 31u;
-    window = (((uint64_t)load_be(S.words, i) << 32) | load_be(S.words, i + 1)) << off;
-    avail = 64 - (int)off;
-    next_word = i + 2;
+    widx = p >> 5;
+    w0 = load_be(S.words, widx), w1 = load_be(S.words, widx + 1), w2 = load_be(S.words, widx + 2);
   };
   if (p < limit) reload();
+  // The body has no data-dependent branches apart from the rare cases (a code longer than the
+  // look-up, a restart boundary, the end of the stream, the end of a block): the 32 lanes of a
+  // warp sit at unrelated places of their blocks, and every divergent path is paid by all.
   while (p < limit) {
-    const uint32_t bits = (uint32_t)(window >> 32);
-    const int comp = T.blk_comp[b];
-    int sym, len;
-    huff_lookup(T, z == 0 ? T.blk_dc[b] : T.blk_ac[b], bits, sym, len);
-    const int s = sym & 15;  // DC: the category itself (<= 11 for 8-bit data); AC: low nibble
-    const uint32_t used = (uint32_t)(len + s);
-    if (p + used > S.total_bits) {  // the padding at the very end: nothing more to decode
-      p = S.total_bits;
-      break;
-    }
-    if (p + used > next_bound) {  // ran into the padding before a restart marker: new segment
+    const uint32_t bits = __funnelshift_l(w1, w0, p);
+    const bool dc_mode = z == 0;
+    const uint32_t slot = dc_mode ? (info >> 8) & 255u : info >> 16;
+    uint32_t e = T.lut[slot][bits >> (32 - kLutBits)];
+    if (e == 0) e = huff_slow(T, (int)slot, bits);
+    const uint32_t used = e & 255u, len = (e >> 8) & 255u, shift = (e >> 16) & 255u;
+    const uint32_t p_next = p + used;
+    if (p_next > stop) {
+      if (p_next > S.total_bits) {  // the padding at the very end: nothing more to decode
+        p = S.total_bits;
+        break;
+      }
+      // ran into the padding before a restart marker: new segment
       p = next_bound, b = 0, z = 0, agg.flag = 1;
-      dc[0] = dc[1] = dc[2] = 0;
+      dc0 = dc1 = dc2 = 0;
       ++j;
       next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
+      stop = min(S.total_bits, next_bound);
+      info = T.blk_info[0];
       if (p < limit) reload();
       continue;
     }
-    const int value = s ? extend((bits << len) >> (32 - s), s) : 0;
-    p += used;
-    window <<= used;
-    avail -= (int)used;
-    if (avail < 32) {
-      window |= (uint64_t)load_be(S.words, next_word) << (32 - avail);
-      ++next_word;
-      avail += 32;
+    // EXTEND (T.81 F.2.2.1): magnitude bits with a leading 0 mean value - (2^s - 1); s = 0 gives 0
+    const uint32_t tail = bits << len;
+    const int raw = (int)__funnelshift_rc(tail, 0u, shift);
+    const int value = raw + (~((int)tail >> 31) & (1 - (int)(1u << (32u - shift))));
+    if ((p_next ^ p) >> 5) {  // crossed into the next word
+      w0 = w1, w1 = w2;
+      ++widx;
+      w2 = load_be(S.words, widx + 2);
     }
-    if (z == 0) {
-      dc[comp] += value;
-      if (kWrite && blk < total_blocks) coef[(size_t)blk * 64] = (int16_t)dc[comp];
-      z = 1;
-    } else if (s == 0) {
-      z = (sym >> 4) == 15 ? z + 16 : 64;
-    } else {
-      z += sym >> 4;
-      if (kWrite && z < 64 && blk < total_blocks) coef[(size_t)blk * 64 + T.natural[z]] = (int16_t)value;
-      ++z;
+    p = p_next;
+    const uint32_t comp = info & 255u;
+    const int add = dc_mode ? value : 0;
+    dc0 += comp == 0 ? add : 0;
+    dc1 += comp == 1 ? add : 0;
+    dc2 += comp == 2 ? add : 0;
+    const int zn = z + (int)(e >> 24);
+    if (kWrite) {
+      // every stored symbol lands at zig-zag index zn - 1 (the DC at 0); ZRL / EOB store nothing
+      if ((dc_mode || shift != 32u) && zn <= 64 && blk < total_blocks)
+        blk_ptr[T.natural[(zn - 1) & 63]] = (int16_t)(dc_mode ? (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) : value);
     }
-    if (z >= 64) {
+    z = zn;
+    if (zn >= 64) {  // block complete
       z = 0;
-      ++agg.nb;
-      if (kWrite) ++blk;
+      ++nb;
+      if (kWrite) ++blk, blk_ptr += 64;
       b = b + 1 == S.bpm ? 0 : b + 1;
+      info = T.blk_info[b];
     }
   }
+  agg.nb += nb;
   if (p >= S.total_bits) p = S.total_bits, b = 0, z = 0;  // one canonical state past the end
-  agg.d0 = dc[0], agg.d1 = dc[1], agg.d2 = dc[2];
+  agg.d0 = dc0, agg.d1 = dc1, agg.d2 = dc2;
   p_io = p, b_io = b, z_io = z;
 }
 
+// Slots 0..2: the DC table of component 0..2; slots 3..5: the AC tables.  (Components sharing
+// a table get identical copies: simpler than a mapping, and the copies are built in parallel.)
 __device__ __forceinline__ void build_tables(const ia_jpeg_job& J, HuffTables& T) {
   const int tid = threadIdx.x;
-  for (int i = tid; i < 8 * (1 << kLutBits); i += kHuffThreads) (&T.lut[0][0])[i] = 0;
-  for (int i = tid; i < 8 * 256; i += kHuffThreads) {
-    const int t = i >> 8, k = i & 255;
-    T.vals[t][k] = t < 4 ? (k < 16 ? J.dc_vals[t][k] : 0) : J.ac_vals[t - 4][k];
+  for (int i = tid; i < kHuffSlots * (1 << kLutBits); i += kHuffThreads) (&T.lut[0][0])[i] = 0;
+  for (int i = tid; i < kHuffSlots * 256; i += kHuffThreads) {
+    const int slot = i >> 8, k = i & 255, c = slot % 3;
+    uint8_t v = 0;
+    if (c < J.ncomp) v = slot < 3 ? (k < 16 ? J.dc_vals[J.comp_dc[c]][k] : 0) : J.ac_vals[J.comp_ac[c]][k];
+    T.vals[slot][k] = v;
   }
   __syncthreads();
-  if (tid < 8) {
-    const uint8_t* counts = tid < 4 ? J.dc_counts[tid] : J.ac_counts[tid - 4];
+  if (tid < kHuffSlots) {
+    const int slot = tid, c = slot % 3;
+    const uint8_t* counts = slot < 3 ? J.dc_counts[J.comp_dc[c < J.ncomp ? c : 0]] : J.ac_counts[J.comp_ac[c < J.ncomp ? c : 0]];
     int code = 0, k = 0;
     for (int l = 1; l <= 16; ++l) {
-      const int cnt = counts[l - 1];
-      T.valoff[tid][l] = k - code;
-      for (int c = 0; c < cnt; ++c, ++k, ++code) {
+      const int cnt = c < J.ncomp ? counts[l - 1] : 0;
+      T.valoff[slot][l] = k - code;
+      for (int n = 0; n < cnt; ++n, ++k, ++code) {
         if (l <= kLutBits) {
-          const uint16_t e = (uint16_t)((l << 8) | T.vals[tid][k & 255]);
+          const uint32_t e = pack_entry(slot, l, T.vals[slot][k & 255]);
           const int first = code << (kLutBits - l);
-          for (int f = 0; f < (1 << (kLutBits - l)); ++f) T.lut[tid][(first + f) & ((1 << kLutBits) - 1)] = e;
+          for (int f = 0; f < (1 << (kLutBits - l)); ++f) T.lut[slot][(first + f) & ((1 << kLutBits) - 1)] = e;
         }
       }
       // codes of this length are < maxcode (left-aligned to 16 bits); a length without codes
       // inherits the previous bound so that it never matches
-      T.maxcode[tid][l] = cnt ? (code << (16 - l)) : (l > 1 ? T.maxcode[tid][l - 1] : 0);
+      T.maxcode[slot][l] = cnt ? (code << (16 - l)) : (l > 1 ? T.maxcode[slot][l - 1] : 0);
       code <<= 1;
     }
   } else if (tid >= 32 && tid < 48) {
     const int i = tid - 32;
     const int k = i < J.blocks_per_mcu ? i : 0;
     const int c = J.block_comp[k];
-    T.blk_comp[i] = (uint8_t)c;
-    T.blk_dc[i] = J.comp_dc[c];
-    T.blk_ac[i] = (uint8_t)(4 + J.comp_ac[c]);
+    T.blk_info[i] = (uint32_t)c | ((uint32_t)c << 8) | ((uint32_t)(3 + c) << 16);
   } else if (tid >= 64 && tid < 128) {
     constexpr uint8_t kNatural[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,
                                       12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6,  7,  14, 21, 28,
@@ -398,8 +414,7 @@ __device__ __forceinline__ void build_tables(const ia_jpeg_job& J, HuffTables& T
 __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job* __restrict__ jobs, int max_chunks,
                                                                uint32_t* __restrict__ ticket_counter,
                                                                int32_t* __restrict__ status) {
-  extern __shared__ __align__(16) unsigned char huff_smem[];
-  HuffTables& T = *reinterpret_cast<HuffTables*>(huff_smem);
+  __shared__ HuffTables T;
   // per subsequence: assumed entry state, resulting exit state and contribution
   __shared__ uint32_t s_entry_p[kHuffThreads], s_entry_bz[kHuffThreads];
   __shared__ uint32_t s_exit_p[kHuffThreads], s_exit_bz[kHuffThreads];
@@ -475,8 +490,18 @@ __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job
   };
   s_entry_p[tid] = min(chunk_begin + (uint32_t)tid * kSubseqBits, S.total_bits);  // a guess (exact for
   s_entry_bz[tid] = 0;                                                             // chunk 0, thread 0)
+  auto now_us = []() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return (uint32_t)(t >> 10);  // ~microseconds
+  };
+  uint32_t t_mark[6];  // diagnostics (thread 0): phase boundaries
+  t_mark[0] = now_us();
   run(tid);
+  __syncthreads();
+  t_mark[1] = now_us();
   converge(false);
+  t_mark[2] = now_us();
 
   // Hand-over between the chunks of one image.  Record of a chunk (kChainWords words):
   //   [0] tentative flag, [1..2] exit state after converging on guesses — right with near
@@ -537,6 +562,7 @@ __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job
     __syncthreads();
   };
   local_scan();
+  t_mark[3] = now_us();
 
   // the predecessor's final record: running totals, and a check of the state this chunk assumed
   if (tid == 0) {
@@ -556,6 +582,7 @@ __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job
     converge(true);
     local_scan();
   }
+  t_mark[4] = now_us();
   Agg before = s_carry;  // everything before this thread: carry (+) earlier warps (+) earlier lanes
   if (warp > 0) before = combine(before, s_warp_agg[warp - 1]);
   {
@@ -580,6 +607,11 @@ __global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job
   int b = (int)(s_entry_bz[tid] >> 8), z = (int)(s_entry_bz[tid] & 255u);
   decode_range<true>(S, T, p, b, z, chunk_begin + (uint32_t)(tid + 1) * kSubseqBits, w, before.nb, J.coef_dev,
                      J.total_blocks);
+  __syncthreads();
+  if (tid == 0) {  // phase durations for tools: guesses, repeats, repair, wait for the chain, write
+    t_mark[5] = now_us();
+    for (int k = 0; k < 5; ++k) my_rec[11 + k] = t_mark[k + 1] - t_mark[k];
+  }
 }
 
 // =================================================================================== IDCT
@@ -720,20 +752,50 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
   const int x0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * kColourPixels, y = blockIdx.y * 8 + (threadIdx.x >> 5);
   const int W = J.width, H = J.height;
   if (x0 >= W || y >= H) return;
-  const int pitch_y = J.mcux * J.h[0] * 8;
-  const uint8_t* __restrict__ yrow = J.plane_dev[0] + (size_t)y * pitch_y;
+  const uint8_t* __restrict__ yrow = J.plane_dev[0] + (size_t)y * J.comp_pitch[0];
   const int ncomp = J.ncomp, orientation = J.orientation;
-  int hexp[2] = {1, 1}, vexp[2] = {1, 1}, dw[2] = {0, 0}, dh[2] = {0, 0}, pitch[2] = {0, 0};
+  const int count = min(kColourPixels, W - x0);
+  // chroma of the four pixels.  Interior groups of the common layouts (4:2:0, 4:2:2, 4:4:4) use
+  // four bytes per chroma row; everything else (image borders, other factors, tiny planes)
+  // goes pixel by pixel through chroma_sample.
+  int chroma[2][kColourPixels];
   if (ncomp == 3) {
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-      hexp[k] = J.hmax / J.h[k + 1], vexp[k] = J.vmax / J.v[k + 1];
-      dw[k] = (W * J.h[k + 1] + J.hmax - 1) / J.hmax, dh[k] = (H * J.v[k + 1] + J.vmax - 1) / J.vmax;
-      pitch[k] = J.mcux * J.h[k + 1] * 8;
+      const int hexp = J.hexp[k + 1], vexp = J.vexp[k + 1], dw = J.comp_w[k + 1], dh = J.comp_h[k + 1];
+      const int pitch = J.comp_pitch[k + 1];
+      const uint8_t* __restrict__ plane = J.plane_dev[k + 1];
+      const int xc = x0 >> 1;
+      if (hexp == 2 && vexp <= 2 && count == kColourPixels && xc >= 1 && xc + 2 <= dw - 1 && dw > 2) {
+        const int yc = vexp == 2 ? y >> 1 : y;
+        int yo = yc;
+        if (vexp == 2) {
+          yo = (y & 1) ? yc + 1 : yc - 1;
+          yo = yo < 0 ? 0 : (yo > dh - 1 ? dh - 1 : yo);
+        }
+        const uint8_t* r0 = plane + (size_t)yc * pitch + xc - 1;
+        const uint8_t* r1 = plane + (size_t)yo * pitch + xc - 1;
+        int cs[4];  // h2v2: 3 * near row + far row ("colsum"); h2v1: the sample itself
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cs[i] = vexp == 2 ? 3 * r0[i] + r1[i] : r0[i];
+        if (vexp == 2) {
+          chroma[k][0] = (3 * cs[1] + cs[0] + 8) >> 4, chroma[k][1] = (3 * cs[1] + cs[2] + 7) >> 4;
+          chroma[k][2] = (3 * cs[2] + cs[1] + 8) >> 4, chroma[k][3] = (3 * cs[2] + cs[3] + 7) >> 4;
+        } else {
+          chroma[k][0] = (3 * cs[1] + cs[0] + 1) >> 2, chroma[k][1] = (3 * cs[1] + cs[2] + 2) >> 2;
+          chroma[k][2] = (3 * cs[2] + cs[1] + 1) >> 2, chroma[k][3] = (3 * cs[2] + cs[3] + 2) >> 2;
+        }
+      } else if (hexp == 1 && vexp == 1) {
+#pragma unroll
+        for (int i = 0; i < kColourPixels; ++i) chroma[k][i] = plane[(size_t)y * pitch + min(x0 + i, W - 1)];
+      } else {
+#pragma unroll
+        for (int i = 0; i < kColourPixels; ++i)
+          chroma[k][i] = chroma_sample(plane, pitch, dw, dh, hexp, vexp, min(x0 + i, W - 1), y);
+      }
     }
   }
   uint8_t rgb[kColourPixels * 3];
-  const int count = min(kColourPixels, W - x0);
 #pragma unroll
   for (int i = 0; i < kColourPixels; ++i) {
     const int x = min(x0 + i, W - 1);
@@ -742,8 +804,7 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
     if (ncomp == 1) {
       r = g = b = yy;
     } else {
-      const int cb = chroma_sample(J.plane_dev[1], pitch[0], dw[0], dh[0], hexp[0], vexp[0], x, y) - 128;
-      const int cr = chroma_sample(J.plane_dev[2], pitch[1], dw[1], dh[1], hexp[1], vexp[1], x, y) - 128;
+      const int cb = chroma[0][i] - 128, cr = chroma[1][i] - 128;
       // jdcolor.c build_ycc_rgb_table: FIX(1.40200)=91881, FIX(1.77200)=116130,
       // FIX(0.71414)=46802, FIX(0.34414)=22554, ONE_HALF=32768, arithmetic shifts
       r = yy + ((91881 * cr + 32768) >> 16);

@@ -31,7 +31,9 @@ class JpegJob(ctypes.Structure):
     _fields_ = [
         ("width", c_int32), ("height", c_int32), ("out_width", c_int32), ("out_height", c_int32),
         ("orientation", c_int32), ("ncomp", c_int32), ("h", c_int32 * 3), ("v", c_int32 * 3),
-        ("hmax", c_int32), ("vmax", c_int32), ("mcux", c_int32), ("mcuy", c_int32),
+        ("hmax", c_int32), ("vmax", c_int32), ("comp_w", c_int32 * 3), ("comp_h", c_int32 * 3),
+        ("comp_pitch", c_int32 * 3), ("hexp", c_int32 * 3), ("vexp", c_int32 * 3),
+        ("mcux", c_int32), ("mcuy", c_int32),
         ("blocks_per_mcu", c_int32), ("total_blocks", c_int32), ("restart_interval", c_int32),
         ("num_segments", c_int32), ("scan_offset", c_uint32), ("file_bytes", c_uint32),
         ("block_comp", c_uint8 * 12), ("block_bx", c_uint8 * 12), ("block_by", c_uint8 * 12),

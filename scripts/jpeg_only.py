@@ -36,3 +36,4 @@ print(f"{batch_n} x {w}x{h} q{q} ({kb:.0f} KB/file): kernels {ms:.3f} ms -> {bat
 rec = batch.chain_records(0).cpu().numpy()
 live = rec[rec[:, 3] == 1]
 print("chunks", len(live), "rounds", (live[:, 10] & 0xffff).tolist(), "tasks", ((live[:, 10] >> 16) & 0xffff).tolist())
+print("phase us [guess, repeats, repair, chain wait, write] per chunk:", live[:, 11:16].tolist())
