@@ -103,44 +103,96 @@ class JpegBatch:
         return self.workspace[off:off + j.total_blocks * 128].view(torch.int16).view(j.total_blocks, 64)
 
 
+class JpegDecoder:
+    """Reusable decoder for one device: keeps two pinned staging buffers (compressed bytes +
+    job records travel in one host-to-device copy each) and the device workspace between
+    calls, so that a call costs the header parse, one memcpy into pinned memory and the
+    launches.  Calls are ordered on the current stream; use one decoder per stream.  The
+    workspace-backed views of a returned batch (``coefficients``, ``chain_records``) are valid
+    until the next ``decode`` on this decoder; ``frames`` are fresh tensors owned by the caller."""
+
+    def __init__(self, device: torch.device | str | None = None) -> None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("JpegDecoder needs a CUDA device (no CPU fallback in this path)")
+        dev = torch.device(device if device is not None else "cuda")
+        self.device = dev if dev.index is not None else torch.device("cuda", torch.cuda.current_device())
+        self._handle = _bind()
+        self._staging = [None, None]  # pinned uint8 tensors
+        self._busy = [None, None]  # event after the last copy out of each
+        self._turn = 0
+        self._workspace = None
+
+    def _pinned(self, need: int) -> torch.Tensor:
+        self._turn ^= 1
+        k = self._turn
+        if self._busy[k] is not None:
+            self._busy[k].synchronize()  # the copy out of this buffer two calls ago
+        if self._staging[k] is None or self._staging[k].numel() < need:
+            self._staging[k] = torch.empty(max(need, 1 << 20) * 5 // 4, dtype=torch.uint8, pin_memory=True)
+        return self._staging[k]
+
+    def decode(self, blobs: list[bytes]) -> JpegBatch:
+        handle, dev = self._handle, self.device
+        n = len(blobs)
+        jobs = (JpegJob * max(n, 1))()
+        for i, blob in enumerate(blobs):
+            if not blob:
+                raise ValueError("Failed to decode image from bytes: empty input")
+            rc = handle.ia_jpeg_parse(ctypes.cast(ctypes.c_char_p(blob), c_void_p), len(blob), ctypes.byref(jobs[i]))
+            if rc == IA_ERR_UNSUPPORTED:
+                raise UnsupportedJpeg("Failed to decode image from bytes: JPEG flavour not supported on the "
+                                      "device (progressive / arithmetic / 12-bit / CMYK / multi-scan)")
+            if rc != 0:
+                raise ValueError("Failed to decode image from bytes")
+        if n == 0:
+            return JpegBatch(jobs, [], torch.empty(0, dtype=torch.int32, device=dev), None, None)
+        job_bytes = n * ctypes.sizeof(JpegJob)
+        offsets, total = [], (job_bytes + 255) & ~255  # job records first, then the files
+        for blob in blobs:
+            offsets.append(total)
+            total += (len(blob) + 31) & ~15
+        staging = self._pinned(total)
+        host = staging.numpy()
+        for off, blob in zip(offsets, blobs):
+            host[off:off + len(blob)] = np.frombuffer(blob, dtype=np.uint8)
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream(dev)
+            upload = torch.empty(total, dtype=torch.uint8, device=dev)
+            frames = [torch.empty((jobs[i].out_height, jobs[i].out_width, 3), dtype=torch.uint8, device=dev)
+                      for i in range(n)]
+            need = handle.ia_jpeg_workspace_bytes(jobs, n)
+            if self._workspace is None or self._workspace.numel() < need:
+                self._workspace = torch.empty(need * 5 // 4, dtype=torch.uint8, device=dev)
+            workspace = self._workspace
+            file_ptrs = (c_void_p * n)(*[upload.data_ptr() + off for off in offsets])
+            out_ptrs = (c_void_p * n)(*[f.data_ptr() for f in frames])
+            check(handle.ia_jpeg_plan(jobs, n, file_ptrs, out_ptrs, workspace.data_ptr(), workspace.numel()),
+                  "ia_jpeg_plan")
+            ctypes.memmove(staging.data_ptr(), ctypes.addressof(jobs), job_bytes)  # planned records
+            upload.copy_(staging[:total], non_blocking=True)
+            self._busy[self._turn] = torch.cuda.Event()
+            self._busy[self._turn].record(stream)
+            status = torch.empty(n, dtype=torch.int32, device=dev)
+            check(handle.ia_jpeg_decode(jobs, upload.data_ptr(), n, status.data_ptr(), stream.cuda_stream),
+                  "ia_jpeg_decode")
+        return JpegBatch(jobs, frames, status, workspace, upload, upload[:job_bytes])
+
+
+_decoders: dict = {}
+
+
 def decode_jpeg_batch_cuda(blobs: list[bytes], device: torch.device | str | None = None) -> JpegBatch:
-    """Decode ``blobs`` (whole JPEG files) on ``device``; ``.frames[i]`` is uint8 [H, W, 3] RGB."""
+    """Decode ``blobs`` (whole JPEG files) on ``device``; ``.frames[i]`` is uint8 [H, W, 3] RGB.
+    Uses one cached :class:`JpegDecoder` per (device, current stream)."""
     if not torch.cuda.is_available():
         raise RuntimeError("decode_jpeg_batch_cuda needs a CUDA device (no CPU fallback in this path)")
-    handle = _bind()
     dev = torch.device(device if device is not None else "cuda")
     if dev.index is None:
         dev = torch.device("cuda", torch.cuda.current_device())
-    n = len(blobs)
-    jobs = (JpegJob * max(n, 1))()
-    for i, blob in enumerate(blobs):
-        jobs[i] = parse_jpeg(blob)
-    if n == 0:
-        return JpegBatch(jobs, [], torch.empty(0, dtype=torch.int32, device=dev), None, None)
-    offsets, total = [], 0
-    for blob in blobs:
-        offsets.append(total)
-        total += (len(blob) + 31) & ~15
-    staging = torch.empty(total, dtype=torch.uint8, pin_memory=True)
-    host = staging.numpy()
-    for off, blob in zip(offsets, blobs):
-        host[off:off + len(blob)] = np.frombuffer(blob, dtype=np.uint8)
-    with torch.cuda.device(dev):
-        files_dev = staging.to(dev, non_blocking=True)
-        frames = [torch.empty((jobs[i].out_height, jobs[i].out_width, 3), dtype=torch.uint8, device=dev)
-                  for i in range(n)]
-        need = handle.ia_jpeg_workspace_bytes(jobs, n)
-        workspace = torch.empty(need, dtype=torch.uint8, device=dev)
-        file_ptrs = (c_void_p * n)(*[files_dev.data_ptr() + off for off in offsets])
-        out_ptrs = (c_void_p * n)(*[f.data_ptr() for f in frames])
-        check(handle.ia_jpeg_plan(jobs, n, file_ptrs, out_ptrs, workspace.data_ptr(), need), "ia_jpeg_plan")
-        jobs_host = torch.from_numpy(np.frombuffer(bytes(jobs), dtype=np.uint8)[: n * ctypes.sizeof(JpegJob)].copy())
-        jobs_dev = jobs_host.pin_memory().to(dev, non_blocking=True)
-        status = torch.empty(n, dtype=torch.int32, device=dev)
-        check(handle.ia_jpeg_decode(jobs, jobs_dev.data_ptr(), n, status.data_ptr(),
-                                    torch.cuda.current_stream(dev).cuda_stream), "ia_jpeg_decode")
-        jobs_dev.record_stream(torch.cuda.current_stream(dev))
-    return JpegBatch(jobs, frames, status, workspace, files_dev, jobs_dev)
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    if key not in _decoders:
+        _decoders[key] = JpegDecoder(dev)
+    return _decoders[key].decode(blobs)
 
 
 def load_jpeg_from_bytes(image_bytes: bytes) -> np.ndarray:
