@@ -331,6 +331,39 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
                                                "achieved_gbs": by / ms / 1e6,
                                                "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
         del lg
+    # ---- N3: baseline JPEG decode on the device, 64 x 1080p 4:2:0 quality 90.  Not an
+    # HBM-bound stage (Huffman decoding is latency-bound); algorithmic bytes = file in + RGB out
+    try:
+        import cv2  # encoder for the synthetic files, and the host decoder timed beside the GPU
+        import numpy as np
+
+        from shared.processing import jpeg as J
+        from workloads import jpeg_cases as W
+        files = [W.encode(W.photo(1080, 1920, seed=i), 90, "420") for i in range(8)]
+        blobs = [files[i % 8] for i in range(64)]
+        batch = J.decode_jpeg_batch_cuda(blobs, dev)
+        torch.cuda.synchronize(dev)
+        ok = int(batch.status.sum().item()) == 0
+        ms = time_loop(batch.rerun, max(steps // 4, 10), 3, dev)
+        t0 = time.perf_counter()
+        reps = 5
+        for _ in range(reps):
+            last = J.decode_jpeg_batch_cuda(blobs, dev)
+        torch.cuda.synchronize(dev)
+        call_ms = (time.perf_counter() - t0) / reps * 1e3
+        t0 = time.perf_counter()
+        for b in files:
+            cv2.cvtColor(cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR), cv2.COLOR_BGR2RGB)
+        cpu_ms = (time.perf_counter() - t0) / len(files) * 1e3
+        by = sum(len(b) for b in blobs) + 64 * 1080 * 1920 * 3
+        out["N3_jpeg_decode_64x1080p"] = {
+            "images_per_s": 64 / ms * 1e3, "ms": ms, "status_ok": ok, "file_kb": sum(map(len, files)) / 8 / 1024,
+            "algorithmic_bytes": by, "achieved_gbs": by / ms / 1e6, "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs,
+            "from_host_bytes_images_per_s": 64 / call_ms * 1e3, "from_host_bytes_ms": call_ms,
+            "cv2_imdecode_one_core_ms_per_image": cpu_ms}
+        del batch, last
+    except ImportError as e:  # no encoder for the synthetic files on this box
+        out["N3_jpeg_decode_64x1080p"] = {"skipped": str(e)}
     return out
 
 

@@ -7,7 +7,8 @@ Run in the build container (the only place ``/root/reference`` exists):
 
 It imports the reference's own modules (``src/shared/processing/*``,
 ``src/shared/data/curator.py``, ``architectures/monolithic/app/postprocess.py``,
-``architectures/microservices/classification/app/inference.py``),
+``architectures/microservices/classification/app/inference.py``; for JPEG decode
+``load_image_from_bytes`` on files encoded by ``workloads/jpeg_cases.py``),
 feeds them the seeded inputs of ``workloads/synth.py`` and stores what they return in
 ``golden.npz`` (small arrays verbatim; large tensors as SHA-256 of their bytes plus a
 strided sample).  Nothing at test/bench time reads ``/root/reference``; the tests read
@@ -208,6 +209,27 @@ def main() -> None:
             probs.append([t[2] for t in top])
         out[f"{name}_ids"] = np.array(ids, dtype=np.int64)
         out[f"{name}_probs"] = np.array(probs, dtype=np.float64)  # float(probs[idx]) of f32 values
+
+    # ---- N3: baseline JPEGs through the reference's own load_image_from_bytes --------------
+    from shared.processing.transforms import load_image_from_bytes
+    from workloads import jpeg_cases
+
+    meta["jpeg"] = []
+    cases = [((40, 56), "420", 85, {}), ((33, 17), "444", 60, {"restart": 2}), ((24, 40), "422", 90, {"optimize": True}),
+             ((17, 33), "440", 30, {}), ((20, 30), "411", 75, {}), ((19, 23), "gray", 80, {}),
+             ((24, 40), "420", 85, {"orientation": 6}), ((96, 128), "420", 95, {})]
+    for i, (shape, sampling, q, kw) in enumerate(cases):
+        kw = dict(kw)
+        orientation = kw.pop("orientation", None)
+        img = jpeg_cases.photo(*shape, seed=700 + i)
+        data = (jpeg_cases.encode(img[..., 0], q, **kw) if sampling == "gray"
+                else jpeg_cases.encode(img, q, sampling, **kw))
+        if orientation:
+            data = jpeg_cases.with_exif_orientation(data, orientation)
+        rgb = load_image_from_bytes(data)
+        out[f"jpeg{i}_bytes"] = np.frombuffer(data, dtype=np.uint8)
+        out[f"jpeg{i}_rgb"] = rgb
+        meta["jpeg"].append({"shape": list(rgb.shape), "sampling": sampling, "quality": q, "sha": sha(rgb)})
 
     out["meta_json"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
     np.savez_compressed(HERE / "golden.npz", **out)

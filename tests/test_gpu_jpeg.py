@@ -61,6 +61,17 @@ def test_pixels_match_oracle(M, shape, sampling):
         assert np.array_equal(got.cpu().numpy(), want)
 
 
+def test_reference_fixtures(M, golden):
+    """The committed files, decoded by the unmodified reference when the fixtures were made."""
+    cases = golden.meta["jpeg"]
+    blobs = [golden[f"jpeg{i}_bytes"].tobytes() for i in range(len(cases))]
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0] * len(cases)
+    for i, frame in enumerate(batch.frames):
+        assert np.array_equal(frame.cpu().numpy(), golden[f"jpeg{i}_rgb"]), cases[i]
+
+
 def test_grayscale(M):
     blobs = [W.encode(W.photo(*shape, seed=3)[..., 0], 80) for shape in ((20, 30), (7, 9), (31, 250))]
     batch = M.decode_jpeg_batch_cuda(blobs)

@@ -41,6 +41,18 @@ def test_exif_orientation(orientation):
         assert want.shape[:2] == (40, 24)
 
 
+def test_reference_fixtures(golden):
+    """Files and pixels committed by tests/golden/make_golden.py: the unmodified reference's
+    load_image_from_bytes (transforms.py:77-110) decoded these bytes to these arrays."""
+    cases = golden.meta["jpeg"]
+    assert len(cases) >= 8
+    for i, case in enumerate(cases):
+        data = golden[f"jpeg{i}_bytes"].tobytes()
+        got = J.load_image_from_bytes(data)
+        assert list(got.shape) == case["shape"] and got.dtype == np.uint8 and got.flags.c_contiguous
+        assert np.array_equal(got, golden[f"jpeg{i}_rgb"]), case
+
+
 def test_rejects():
     with pytest.raises(J.UnsupportedJpeg):
         J.parse(W.encode(W.photo(16, 16, 1), 90, "420", progressive=True))
