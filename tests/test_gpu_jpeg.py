@@ -140,6 +140,37 @@ def test_errors(M):
     assert M.decode_jpeg_batch_cuda([]).frames == []
 
 
+@pytest.mark.timeout(300)
+def test_corrupt_streams_terminate(M):
+    """Damaged entropy data (flipped bytes, inserted markers, cuts) must neither hang nor fault:
+    every call returns frames of the header's size, and a clean file decodes exactly afterwards.
+    (The pixels of a damaged file are not compared: libjpeg's error concealment is out of scope.)"""
+    rng = np.random.default_rng(11)
+    good = W.encode(W.photo(120, 200, seed=4), 85, "420", restart=5)
+    start = J.parse(good)["scan_start"]
+    blobs = []
+    for k in range(24):
+        b = bytearray(good)
+        for _ in range(1 + k % 7):
+            pos = int(rng.integers(start, len(b) - 2))
+            if k % 3 == 0:
+                b[pos] = int(rng.integers(0, 256))
+            elif k % 3 == 1:
+                b[pos:pos + 2] = bytes([0xFF, int(rng.integers(0xD0, 0xD8))])  # stray restart marker
+            else:
+                b[pos] = 0xFF  # FF followed by whatever comes next
+        if k % 4 == 3:
+            b = b[: int(rng.integers(start + 1, len(b)))]
+        blobs.append(bytes(b))
+    blobs.append(good[:start])  # headers only, empty scan
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    for f in batch.frames:
+        assert tuple(f.shape) == (120, 200, 3)
+    assert len(batch.status.cpu().tolist()) == len(blobs)
+    assert np.array_equal(M.load_jpeg_from_bytes(good), W.reference_decode(good))
+
+
 def test_truncated_stream_is_flagged(M):
     data = W.encode(W.photo(64, 64, seed=2), 90, "420")
     batch = M.decode_jpeg_batch_cuda([data[: len(data) * 2 // 3]])
