@@ -501,6 +501,36 @@ def run_gpu_arm(args) -> None:
             dist.destroy_process_group()
         return
 
+    # ---------------- the same leg with the frames arriving as JPEG files ----
+    # What the services actually receive.  Extra information, not the `e2e` key: the boundary
+    # moves one step earlier (the reference decodes with cv2 on the host before the path).
+    e2e_jpeg = None
+    if world == 1 and not args.no_stages:
+        try:
+            from workloads import jpeg_cases as W
+            files = [W.encode(W.photo(SRC_H, SRC_W, seed=i), 90, "420") for i in range(8)]
+            blobs = [files[i % 8] for i in range(B)]
+            for _ in range(2):
+                res = hp.run(blobs, h_heads)
+            t0.record()
+            ticket = None
+            for _ in range(e2e_steps):
+                nxt = hp.submit(blobs, h_heads)
+                if ticket is not None:
+                    res = ticket.wait()
+                ticket = nxt
+            res = ticket.wait()
+            t1.record()
+            torch.cuda.synchronize(dev)
+            jm = t0.elapsed_time(t1)
+            assert int(res["status"].max()) == 0
+            e2e_jpeg = {"value": B * e2e_steps / (jm / 1e3), "unit": UNIT, "h2d_bytes_per_step": hp.last_h2d_bytes,
+                        "d2h_bytes_per_step": hp.d2h_bytes(B), "ms_per_step": jm / e2e_steps,
+                        "jpeg_kb_per_frame": sum(map(len, files)) / 8 / 1024,
+                        "api": "HostPipeline.submit(list_of_jpeg_bytes, heads): files decoded on the device"}
+        except ImportError as e:
+            e2e_jpeg = {"skipped": str(e)}
+
     # ---------------- rank 0 only: stage lines, CPU baseline, parity spot check ----------
     del hp, h_frames, h_heads, frames, head, pipe
     torch.cuda.empty_cache()
@@ -515,6 +545,7 @@ def run_gpu_arm(args) -> None:
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
                 "api": "shared.processing.pipeline.HostPipeline.submit/wait (pinned host buffers in and out, 3 streams x 32-image chunks, 2 batches in flight)"},
+        "e2e_jpeg": e2e_jpeg,
         "gpu_launches": KERNELS_PER_STEP * args.steps,
         "clocks": clocks,
         "rois_per_step": total_rois,

@@ -131,7 +131,9 @@ class JpegDecoder:
             self._staging[k] = torch.empty(max(need, 1 << 20) * 5 // 4, dtype=torch.uint8, pin_memory=True)
         return self._staging[k]
 
-    def decode(self, blobs: list[bytes]) -> JpegBatch:
+    def decode(self, blobs: list[bytes], out: list[torch.Tensor] | None = None) -> JpegBatch:
+        """``out``: optional destination frames (uint8 CUDA tensors [H, W, 3], contiguous, one per
+        file, of exactly the decoded size) instead of fresh ones — e.g. rows of a batch buffer."""
         handle, dev = self._handle, self.device
         n = len(blobs)
         jobs = (JpegJob * max(n, 1))()
@@ -158,8 +160,17 @@ class JpegDecoder:
         with torch.cuda.device(dev):
             stream = torch.cuda.current_stream(dev)
             upload = torch.empty(total, dtype=torch.uint8, device=dev)
-            frames = [torch.empty((jobs[i].out_height, jobs[i].out_width, 3), dtype=torch.uint8, device=dev)
-                      for i in range(n)]
+            if out is None:
+                frames = [torch.empty((jobs[i].out_height, jobs[i].out_width, 3), dtype=torch.uint8, device=dev)
+                          for i in range(n)]
+            else:
+                frames = list(out)
+                if len(frames) != n:
+                    raise ValueError(f"out holds {len(frames)} frames for {n} files")
+                for i, f in enumerate(frames):
+                    want = (jobs[i].out_height, jobs[i].out_width, 3)
+                    if tuple(f.shape) != want or f.dtype != torch.uint8 or not f.is_cuda or not f.is_contiguous():
+                        raise ValueError(f"out[{i}] must be a contiguous CUDA uint8 tensor of shape {want}")
             need = handle.ia_jpeg_workspace_bytes(jobs, n)
             if self._workspace is None or self._workspace.numel() < need:
                 self._workspace = torch.empty(need * 5 // 4, dtype=torch.uint8, device=dev)

@@ -188,6 +188,8 @@ class HostPipeline:
         self._submits = 0
         self._chunks = 0
         self.last_d2h_bytes = 0
+        self.last_h2d_bytes = 0
+        self._decoders = None  # one JpegDecoder per stream slot, created on first JPEG submit
 
     @property
     def h2d_bytes_per_image(self) -> int:
@@ -211,11 +213,18 @@ class HostPipeline:
                 res["crops"][base : base + total].copy_(crops[:total], non_blocking=True)
         self.last_d2h_bytes += total * crops[0].numel() * 4
 
-    def submit(self, frames: torch.Tensor, heads: torch.Tensor) -> HostTicket:
+    def submit(self, frames, heads: torch.Tensor) -> HostTicket:
         """``frames`` uint8 [N,H,W,3] and ``heads`` float32 [N,A,85]: pinned (or pageable) HOST
-        tensors, which must stay untouched until the ticket has been waited on."""
-        n = frames.shape[0]
+        tensors, which must stay untouched until the ticket has been waited on.  ``frames`` may
+        instead be a list of N baseline JPEG files (``bytes``) of the pipeline's frame size: they
+        are uploaded compressed and decoded on the device."""
+        jpeg = isinstance(frames, (list, tuple))
+        n = len(frames) if jpeg else frames.shape[0]
         assert n <= self.max_batch
+        if jpeg and self._decoders is None:
+            from .jpeg import JpegDecoder
+            self._decoders = [JpegDecoder(self.device) for _ in range(self.slots)]
+        self.last_h2d_bytes = 0
         rs = self._submits % self.RESULT_SETS
         self._submits += 1
         if self._tickets[rs] is not None:
@@ -241,8 +250,14 @@ class HostPipeline:
             pipe = self.pipes[slot]
             with torch.cuda.stream(self.streams[slot]):
                 df, dh = self.d_frames[slot][:m], self.d_heads[slot][:m]
-                df.copy_(frames[lo:hi], non_blocking=True)
+                if jpeg:
+                    self._decoders[slot].decode(frames[lo:hi], out=[df[i] for i in range(m)])
+                    self.last_h2d_bytes += sum(len(b) for b in frames[lo:hi])
+                else:
+                    df.copy_(frames[lo:hi], non_blocking=True)
+                    self.last_h2d_bytes += df.numel()
                 dh.copy_(heads[lo:hi], non_blocking=True)
+                self.last_h2d_bytes += dh.numel() * 4
                 out = pipe.run(df, dh)
                 res["roi_offsets"][ci, : m + 1].copy_(out.roi_offsets, non_blocking=True)
                 ev = torch.cuda.Event()
@@ -263,7 +278,7 @@ class HostPipeline:
         self._tickets[rs] = ticket
         return ticket
 
-    def run(self, frames: torch.Tensor, heads: torch.Tensor) -> dict:
+    def run(self, frames, heads: torch.Tensor) -> dict:
         """Synchronous form: returns when every output of the batch is in host memory."""
         return self.submit(frames, heads).wait()
 

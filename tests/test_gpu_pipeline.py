@@ -77,6 +77,32 @@ def test_host_pipeline_sync_and_async():
     assert hp.d2h_bytes(n) > 0 and hp.h2d_bytes_per_image == h * w * 3 + 25200 * 85 * 4
 
 
+def test_host_pipeline_from_jpeg_files():
+    """N3 in the chain: the frames arrive as JPEG files, are decoded on the device into the
+    chunk buffers and run through K1..K4; the oracle sees the same files through the oracle
+    decoder (== cv2.imdecode, tests/test_oracle_jpeg.py)."""
+    from oracle import jpeg as OJ
+    from shared.processing.pipeline import HostPipeline
+    from workloads import jpeg_cases as W
+
+    h, w, n, chunk = 240, 320, 7, 3
+    files = [W.encode(W.photo(h, w, seed=80 + i), 85, "420", restart=(i % 2) * 4) for i in range(n)]
+    frames = np.stack([OJ.load_image_from_bytes(f) for f in files])
+    heads = synth.head_v5(n, seed=81)
+    hp = HostPipeline(n, h, w, "cuda", chunk=chunk, slots=2)
+    want = _oracle(frames, heads)
+    h_heads = torch.from_numpy(heads).pin_memory()
+    _check_host(hp.run(files, h_heads), want, chunk, hp.rpi)
+    t1 = hp.submit(files, h_heads)
+    t2 = hp.submit(torch.from_numpy(frames).pin_memory(), h_heads)  # raw frames through the same pipeline
+    _check_host(t1.wait(), want, chunk, hp.rpi)
+    _check_host(t2.wait(), want, chunk, hp.rpi)
+    assert hp.last_h2d_bytes == frames.nbytes + heads.nbytes
+    with pytest.raises(ValueError):
+        hp.run([W.encode(W.photo(100, 100, seed=1), 85)] * n, h_heads)  # wrong frame size
+    hp.drain()
+
+
 def test_graphed_pipeline_matches_eager():
     """The chain captured in a CUDA graph replays to the same bits, for changing inputs."""
     from shared.processing.pipeline import DevicePipeline, GraphedPipeline
