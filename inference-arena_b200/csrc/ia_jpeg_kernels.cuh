@@ -411,7 +411,7 @@ __device__ __forceinline__ void build_tables(const ia_jpeg_job& J, HuffTables& T
 // predecessor's published record, repairs its first subsequences, publishes its own record and
 // only then writes coefficients.  Tickets are handed out in launch order, so the CTA a chunk
 // waits for is always already running.
-__global__ void __launch_bounds__(kHuffThreads) huffman_kernel(const ia_jpeg_job* __restrict__ jobs, int max_chunks,
+__global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_job* __restrict__ jobs, int max_chunks,
                                                                uint32_t* __restrict__ ticket_counter,
                                                                int32_t* __restrict__ status) {
   __shared__ HuffTables T;
