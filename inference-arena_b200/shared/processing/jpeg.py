@@ -134,7 +134,13 @@ class JpegDecoder:
     def decode(self, blobs: list[bytes], out: list[torch.Tensor] | None = None) -> JpegBatch:
         """``out``: optional destination frames (uint8 CUDA tensors [H, W, 3], contiguous, one per
         file, of exactly the decoded size) instead of fresh ones — e.g. rows of a batch buffer."""
-        handle, dev = self._handle, self.device
+        return self.launch(self.stage(blobs), out)
+
+    def stage(self, blobs: list[bytes]):
+        """Host half of ``decode``: parse the headers and copy the files into pinned memory.
+        Touches no stream, so a worker thread may run it for the next batch while the current
+        one is being launched (at most one ``stage`` ahead of ``launch`` per decoder)."""
+        handle = self._handle
         n = len(blobs)
         jobs = (JpegJob * max(n, 1))()
         for i, blob in enumerate(blobs):
@@ -147,16 +153,26 @@ class JpegDecoder:
             if rc != 0:
                 raise ValueError("Failed to decode image from bytes")
         if n == 0:
-            return JpegBatch(jobs, [], torch.empty(0, dtype=torch.int32, device=dev), None, None)
+            return (jobs, 0, [], 0, None, 0)
         job_bytes = n * ctypes.sizeof(JpegJob)
         offsets, total = [], (job_bytes + 255) & ~255  # job records first, then the files
         for blob in blobs:
             offsets.append(total)
             total += (len(blob) + 31) & ~15
         staging = self._pinned(total)
+        turn = self._turn
         host = staging.numpy()
         for off, blob in zip(offsets, blobs):
             host[off:off + len(blob)] = np.frombuffer(blob, dtype=np.uint8)
+        return (jobs, n, offsets, total, staging, turn)
+
+    def launch(self, staged, out: list[torch.Tensor] | None = None) -> JpegBatch:
+        """Device half of ``decode``: one host-to-device copy and the kernels, on the current stream."""
+        handle, dev = self._handle, self.device
+        jobs, n, offsets, total, staging, turn = staged
+        if n == 0:
+            return JpegBatch(jobs, [], torch.empty(0, dtype=torch.int32, device=dev), None, None)
+        job_bytes = n * ctypes.sizeof(JpegJob)
         with torch.cuda.device(dev):
             stream = torch.cuda.current_stream(dev)
             upload = torch.empty(total, dtype=torch.uint8, device=dev)
@@ -181,8 +197,9 @@ class JpegDecoder:
                   "ia_jpeg_plan")
             ctypes.memmove(staging.data_ptr(), ctypes.addressof(jobs), job_bytes)  # planned records
             upload.copy_(staging[:total], non_blocking=True)
-            self._busy[self._turn] = torch.cuda.Event()
-            self._busy[self._turn].record(stream)
+            busy = torch.cuda.Event()
+            busy.record(stream)
+            self._busy[turn] = busy
             status = torch.empty(n, dtype=torch.int32, device=dev)
             check(handle.ia_jpeg_decode(jobs, upload.data_ptr(), n, status.data_ptr(), stream.cuda_stream),
                   "ia_jpeg_decode")

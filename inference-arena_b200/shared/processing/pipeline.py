@@ -222,8 +222,12 @@ class HostPipeline:
         n = len(frames) if jpeg else frames.shape[0]
         assert n <= self.max_batch
         if jpeg and self._decoders is None:
+            from concurrent.futures import ThreadPoolExecutor
+
             from .jpeg import JpegDecoder
             self._decoders = [JpegDecoder(self.device) for _ in range(self.slots)]
+            # stages the next chunks (one per other stream slot) while chunk i is launched
+            self._stager = ThreadPoolExecutor(max_workers=max(1, self.slots - 1))
         self.last_h2d_bytes = 0
         rs = self._submits % self.RESULT_SETS
         self._submits += 1
@@ -241,23 +245,37 @@ class HostPipeline:
             s.wait_stream(cur)
         used = set()
         pending = None
-        for ci, lo in enumerate(range(0, n, self.chunk)):
+        starts = list(range(0, n, self.chunk))
+        first_chunk = self._chunks
+
+        def stage(ci):  # host half of the JPEG decode of chunk ci (parse + copy into pinned memory)
+            lo = starts[ci]
+            dec = self._decoders[(first_chunk + ci) % self.slots]
+            return self._stager.submit(dec.stage, frames[lo:min(lo + self.chunk, n)])
+
+        ahead = max(1, self.slots - 1)  # chunks i+1 .. i+ahead use the other slots' decoders
+        staged = [stage(ci) for ci in range(min(ahead, len(starts)))] if jpeg else []
+        for ci, lo in enumerate(starts):
             hi = min(lo + self.chunk, n)
             m = hi - lo
             slot = self._chunks % self.slots
             self._chunks += 1
             used.add(slot)
             pipe = self.pipes[slot]
+            if jpeg:
+                ready = staged.pop(0).result()
+                if ci + ahead < len(starts):
+                    staged.append(stage(ci + ahead))
             with torch.cuda.stream(self.streams[slot]):
                 df, dh = self.d_frames[slot][:m], self.d_heads[slot][:m]
+                dh.copy_(heads[lo:hi], non_blocking=True)  # first: the copy engine never waits for a kernel
+                self.last_h2d_bytes += dh.numel() * 4
                 if jpeg:
-                    self._decoders[slot].decode(frames[lo:hi], out=[df[i] for i in range(m)])
+                    self._decoders[slot].launch(ready, out=[df[i] for i in range(m)])
                     self.last_h2d_bytes += sum(len(b) for b in frames[lo:hi])
                 else:
                     df.copy_(frames[lo:hi], non_blocking=True)
                     self.last_h2d_bytes += df.numel()
-                dh.copy_(heads[lo:hi], non_blocking=True)
-                self.last_h2d_bytes += dh.numel() * 4
                 out = pipe.run(df, dh)
                 res["roi_offsets"][ci, : m + 1].copy_(out.roi_offsets, non_blocking=True)
                 ev = torch.cuda.Event()
