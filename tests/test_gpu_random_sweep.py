@@ -88,3 +88,41 @@ def test_k2k3_random_heads(D):
             k = int(count[i])
             assert int(status[i]) == 0 and keep[i, :k].cpu().tolist() == want_keep, (anchors, classes, cand)
             assert np.array_equal(dets[i, :k].cpu().numpy(), want_dets)
+
+
+def test_jpeg_random_files():
+    """Random sizes, sampling modes, qualities, restart intervals, table optimisation, content
+    (photo-like, noise, flat), orientation tags — one mixed batch per round, against cv2.imdecode
+    (the call load_image_from_bytes makes)."""
+    cv2 = pytest.importorskip("cv2")  # noqa: F841
+    from shared.processing import jpeg as J
+    from workloads import jpeg_cases as W
+
+    rng = np.random.default_rng(4321)
+    for rnd in range(3):
+        blobs = []
+        for i in range(20):
+            h, w = int(rng.integers(1, 400)), int(rng.integers(1, 600))
+            kind = int(rng.integers(0, 4))
+            if kind == 0:
+                img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+            elif kind == 1:
+                img = np.full((h, w, 3), rng.integers(0, 256, 3), dtype=np.uint8)
+            else:
+                img = W.photo(h, w, seed=rnd * 100 + i)
+            q = int(rng.integers(1, 101))
+            if rng.random() < 0.15:
+                data = W.encode(img[..., 0], q, restart=int(rng.integers(0, 9)))
+            else:
+                data = W.encode(img, q, W.SAMPLINGS[int(rng.integers(0, 5))], restart=int(rng.integers(0, 9)),
+                                optimize=bool(rng.integers(0, 2)))
+            if rng.random() < 0.3:
+                data = W.with_exif_orientation(data, int(rng.integers(1, 9)), big_endian=bool(rng.integers(0, 2)))
+            blobs.append(data)
+        batch = J.decode_jpeg_batch_cuda(blobs)
+        torch.cuda.synchronize()
+        assert batch.status.cpu().tolist() == [0] * len(blobs)
+        for k, (frame, data) in enumerate(zip(batch.frames, blobs)):
+            want = W.reference_decode(data)
+            assert tuple(frame.shape) == want.shape, (rnd, k)
+            assert np.array_equal(frame.cpu().numpy(), want), (rnd, k)
