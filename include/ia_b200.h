@@ -294,7 +294,7 @@ typedef struct ia_jpeg_job {
   /* --- filled by ia_jpeg_plan (device pointers) --- */
   const uint8_t* file_dev; /* the whole file */
   uint8_t* clean_dev;      /* entropy-coded bytes without stuffing / RST markers */
-  uint32_t* segment_dev;   /* [num_segments + 1] info + restart boundaries (clean byte offsets) */
+  uint32_t* segment_dev;   /* [0] clean bytes, [1] restart boundaries found, [2..] their clean byte offsets */
   int16_t* coef_dev;       /* [total_blocks, 64] natural order, DC absolute, not dequantised */
   uint8_t* plane_dev[IA_JPEG_MAX_COMPONENTS]; /* per component, padded to whole MCUs */
   uint8_t* out_dev;        /* uint8 [out_height, out_width, 3] RGB */
