@@ -282,12 +282,16 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
         continue;
       }
       const YPlan yp = yplan[buf][j];
-#pragma unroll 7
-      for (int x = lane; x < S; x += 32) {
-        const int2 e = xt[x];
+      // one pointer per colour plane, advanced by a constant: under the unroll the stores use
+      // immediate offsets instead of 64-bit address arithmetic per element
+      float* o0 = orow + lane;
+      float* o1 = o0 + plane;
+      float* o2 = o1 + plane;
+      auto pixel = [&](const int2 e, float* d0, float* d1, float* d2) {
         uint32_t lo0, hi0, lo1, hi1;
         load6(stage32, yp.off0 + e.x, lo0, hi0);
         load6(stage32, yp.off1 + e.x, lo1, hi1);
+        float* const dst[3] = {d0, d1, d2};
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           // h = p[c]*a0 + p[c+3]*a1 in one IDP.2A; a zero weight multiplies whatever byte sits
@@ -295,8 +299,16 @@ __global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const Crop
           const int h0 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo0, hi0, c), 0u);
           const int h1 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo1, hi1, c), 0u);
           const int v = vresize(h0, h1, yp.b0, yp.b1);
-          st_stream_f1(orow + c * plane + x, lut[c][v * kLutRep + rep]);
+          st_stream_f1(dst[c], lut[c][v * kLutRep + rep]);
         }
+      };
+      if (S == 7 * 32) {  // MobileNet's 224: a fixed trip count, so every offset is an immediate
+        const int2* xl = xt + lane;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) pixel(xl[32 * k], o0 + 32 * k, o1 + 32 * k, o2 + 32 * k);
+      } else {
+#pragma unroll 4
+        for (int x = lane; x < S; x += 32, o0 += 32, o1 += 32, o2 += 32) pixel(xt[x], o0, o1, o2);
       }
     }
     __syncwarp();
