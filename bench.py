@@ -541,6 +541,27 @@ def run_gpu_arm(args) -> None:
                         "d2h_bytes_per_step": hp.d2h_bytes(B), "ms_per_step": jm / e2e_steps,
                         "jpeg_kb_per_frame": sum(map(len, files)) / 8 / 1024,
                         "api": "HostPipeline.submit(list_of_jpeg_bytes, heads): files decoded on the device"}
+            # and with both models on the GPU: the head never leaves the device, the
+            # model inputs are not copied back; only frames go up and detections come down
+            on_gpu = {}
+            for name, src in (("raw_frames", h_frames), ("jpeg_files", blobs)):
+                for _ in range(2):
+                    res = hp.run(src, head, tensors_to_host=False)
+                t0.record()
+                ticket = None
+                for _ in range(e2e_steps):
+                    nxt = hp.submit(src, head, tensors_to_host=False)
+                    if ticket is not None:
+                        res = ticket.wait()
+                    ticket = nxt
+                res = ticket.wait()
+                t1.record()
+                torch.cuda.synchronize(dev)
+                gm = t0.elapsed_time(t1)
+                assert int(res["status"].max()) == 0
+                on_gpu[name] = {"value": B * e2e_steps / (gm / 1e3), "unit": UNIT, "ms_per_step": gm / e2e_steps,
+                                "h2d_bytes_per_step": hp.last_h2d_bytes, "d2h_bytes_per_step": hp.d2h_bytes(B)}
+            e2e_jpeg["models_on_gpu"] = on_gpu
         except ImportError as e:
             e2e_jpeg = {"skipped": str(e)}
 

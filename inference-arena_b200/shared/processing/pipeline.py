@@ -213,11 +213,16 @@ class HostPipeline:
                 res["crops"][base : base + total].copy_(crops[:total], non_blocking=True)
         self.last_d2h_bytes += total * crops[0].numel() * 4
 
-    def submit(self, frames, heads: torch.Tensor) -> HostTicket:
+    def submit(self, frames, heads: torch.Tensor, tensors_to_host: bool = True) -> HostTicket:
         """``frames`` uint8 [N,H,W,3] and ``heads`` float32 [N,A,85]: pinned (or pageable) HOST
         tensors, which must stay untouched until the ticket has been waited on.  ``frames`` may
         instead be a list of N baseline JPEG files (``bytes``) of the pipeline's frame size: they
-        are uploaded compressed and decoded on the device."""
+        are uploaded compressed and decoded on the device.
+
+        With both models on the GPU nothing big needs to cross PCIe except the
+        frames: ``heads`` may be a CUDA tensor (the detector's output, used in place), and
+        ``tensors_to_host=False`` leaves the two model inputs (``tensor``, ``crops``) on the
+        device — only detections, counts and ROI offsets are copied back."""
         jpeg = isinstance(frames, (list, tuple))
         n = len(frames) if jpeg else frames.shape[0]
         assert n <= self.max_batch
@@ -238,7 +243,7 @@ class HostPipeline:
                 t.finish_last_chunk()
         res = self.results[rs]
         p = self.pipes[0]
-        per_image = 3 * p.target * p.target * 4 + p.max_det * (6 * 4 + 4) + 4 + 4
+        per_image = (3 * p.target * p.target * 4 if tensors_to_host else 0) + p.max_det * (6 * 4 + 4) + 4 + 4
         self.last_d2h_bytes = n * per_image
         cur = torch.cuda.current_stream(self.device)
         for s in self.streams:
@@ -268,8 +273,11 @@ class HostPipeline:
                     staged.append(stage(ci + ahead))
             with torch.cuda.stream(self.streams[slot]):
                 df, dh = self.d_frames[slot][:m], self.d_heads[slot][:m]
-                dh.copy_(heads[lo:hi], non_blocking=True)  # first: the copy engine never waits for a kernel
-                self.last_h2d_bytes += dh.numel() * 4
+                if heads.is_cuda:
+                    dh = heads[lo:hi]
+                else:
+                    dh.copy_(heads[lo:hi], non_blocking=True)  # first: the copy engine never waits for a kernel
+                    self.last_h2d_bytes += dh.numel() * 4
                 if jpeg:
                     self._decoders[slot].launch(ready, out=[df[i] for i in range(m)])
                     self.last_h2d_bytes += sum(len(b) for b in frames[lo:hi])
@@ -280,7 +288,8 @@ class HostPipeline:
                 res["roi_offsets"][ci, : m + 1].copy_(out.roi_offsets, non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record()
-                res["tensor"][lo:hi].copy_(out.tensor, non_blocking=True)
+                if tensors_to_host:
+                    res["tensor"][lo:hi].copy_(out.tensor, non_blocking=True)
                 res["dets"][lo:hi].copy_(out.dets, non_blocking=True)
                 res["keep"][lo:hi].copy_(out.keep, non_blocking=True)
                 res["count"][lo:hi].copy_(out.count, non_blocking=True)
@@ -288,7 +297,7 @@ class HostPipeline:
                 self.last_d2h_bytes += (m + 1) * 4
             if pending is not None:
                 self._copy_crops(pending)  # previous chunk: its total is on the host by now
-            pending = (slot, ev, res, ci, lo, m, out.crops)
+            pending = (slot, ev, res, ci, lo, m, out.crops) if tensors_to_host else None
         views = {"tensor": res["tensor"][:n], "dets": res["dets"][:n], "keep": res["keep"][:n],
                  "count": res["count"][:n], "status": res["status"][:n], "crops": res["crops"],
                  "roi_offsets": res["roi_offsets"]}
@@ -296,9 +305,9 @@ class HostPipeline:
         self._tickets[rs] = ticket
         return ticket
 
-    def run(self, frames, heads: torch.Tensor) -> dict:
+    def run(self, frames, heads: torch.Tensor, tensors_to_host: bool = True) -> dict:
         """Synchronous form: returns when every output of the batch is in host memory."""
-        return self.submit(frames, heads).wait()
+        return self.submit(frames, heads, tensors_to_host).wait()
 
     def drain(self) -> None:
         for t in self._tickets:

@@ -101,6 +101,14 @@ def test_host_pipeline_from_jpeg_files():
     with pytest.raises(ValueError):
         hp.run([W.encode(W.photo(100, 100, seed=1), 85)] * n, h_heads)  # wrong frame size
     hp.drain()
+    # both models on the GPU: the head is already a device tensor, the model inputs stay there
+    res = hp.run(files, torch.from_numpy(heads).cuda(), tensors_to_host=False)
+    for i, (_, dets, keep, _, _) in enumerate(want):
+        k = int(res["count"][i])
+        assert int(res["status"][i]) == 0 and res["keep"][i, :k].tolist() == keep
+        assert np.array_equal(res["dets"][i, :k].numpy(), dets)
+    assert hp.last_h2d_bytes == sum(len(f) for f in files)
+    hp.drain()
 
 
 def test_graphed_pipeline_matches_eager():
