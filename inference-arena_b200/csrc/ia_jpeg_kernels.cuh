@@ -242,7 +242,7 @@ __device__ __forceinline__ Agg shfl_up_agg(const Agg& a, int d) {
 }
 
 // entry for a code longer than the look-up covers
-__device__ __noinline__ uint32_t huff_slow(const HuffTables& T, int slot, uint32_t bits) {
+__device__ __forceinline__ uint32_t huff_slow(const HuffTables& T, int slot, uint32_t bits) {
   const int32_t code = (int32_t)(bits >> 16);
   for (int l = kLutBits + 1; l <= 16; ++l) {
     if (code < T.maxcode[slot][l]) return pack_entry(slot, l, T.vals[slot][(T.valoff[slot][l] + (code >> (16 - l))) & 255]);
