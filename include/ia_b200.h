@@ -68,8 +68,10 @@ int ia_yolo_preprocess(const uint8_t* frames_dev, int n, int src_h, int src_w, i
  * n frames of DIFFERENT sizes in one call — what a service sees with real COCO frames.
  *   frames_host  HOST array of n descriptors (device pointer + height + width per frame)
  *   out_dev      float [n, 3, target, target]; image i comes from frames_host[i]
- * Frames are grouped by shape on the host; each group is one launch whose frame pointers
- * travel in the kernel parameters (no device scratch, no copies, no synchronisation). */
+ * Frames are grouped by shape on the host; the frame pointers and each shape's geometry travel
+ * in the kernel parameters (no device scratch, no copies, no synchronisation).  Up to 32 shapes
+ * and 256 frames are ONE launch (a CTA looks its shape up from its block index); beyond that,
+ * one launch per shape. */
 typedef struct ia_frame_desc {
   const uint8_t* data_dev; /* uint8 [h, w, 3], contiguous */
   int32_t h, w;

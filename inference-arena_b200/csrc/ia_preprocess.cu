@@ -112,29 +112,15 @@ struct PreRagged<true> {
   int out_index[kRaggedMax];
 };
 
-template <bool kOutU8, int kMode, bool kRagged>
-__global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams p,
-                                                                const __grid_constant__ PreRagged<kRagged> rg) {
-  extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(16) float lut[kOutU8 ? 4 : 256 * kPreLutRep];
-  __shared__ RowPlan plan[kPreMaxRows];
-  __shared__ int seg_row[2 * kPreMaxRows];  // source row per (output row, tap), -1 = none
-  __shared__ __align__(8) uint64_t bar;
-
+// The work of one CTA: `rows_per_cta` output rows of one image, starting at y_begin.  The
+// shared arrays belong to the calling kernel (one set, whatever modes it instantiates).
+template <bool kOutU8, int kMode>
+__device__ __forceinline__ void letterbox_body(const PreParams& p, const uint8_t* frame, int out_img, int y_begin,
+                                               uint8_t* smem, float* lut, RowPlan* plan, int* seg_row,
+                                               uint64_t& bar) {
   const int tid = threadIdx.x, lane = tid & 31;
-  const int img = blockIdx.x / p.groups;
-  const int y_begin = (blockIdx.x % p.groups) * p.rows_per_cta;
   const int rows = min(p.rows_per_cta, p.target - y_begin);
   const uint32_t row_bytes = (uint32_t)p.src_w * 3u;
-  const uint8_t* frame;
-  int out_img;
-  if constexpr (kRagged) {
-    frame = rg.frame[img];
-    out_img = rg.out_index[img];
-  } else {
-    frame = p.frames + (size_t)img * p.src_h * row_bytes;
-    out_img = img;
-  }
   int2* xtab = reinterpret_cast<int2*>(smem + (size_t)p.slots_cap * p.slot_bytes);
 
   if (tid == 0) {
@@ -295,6 +281,64 @@ __global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams 
   }
 }
 
+template <bool kOutU8, int kMode, bool kRagged>
+__global__ void __launch_bounds__(kPreThreads) letterbox_kernel(const PreParams p,
+                                                                const __grid_constant__ PreRagged<kRagged> rg) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(16) float lut[kOutU8 ? 4 : 256 * kPreLutRep];
+  __shared__ RowPlan plan[kPreMaxRows];
+  __shared__ int seg_row[2 * kPreMaxRows];  // source row per (output row, tap), -1 = none
+  __shared__ __align__(8) uint64_t bar;
+  const int img = blockIdx.x / p.groups;
+  const int y_begin = (blockIdx.x % p.groups) * p.rows_per_cta;
+  const uint8_t* frame;
+  int out_img;
+  if constexpr (kRagged) {
+    frame = rg.frame[img];
+    out_img = rg.out_index[img];
+  } else {
+    frame = p.frames + (size_t)img * p.src_h * p.src_w * 3u;
+    out_img = img;
+  }
+  letterbox_body<kOutU8, kMode>(p, frame, out_img, y_begin, smem, lut, plan, seg_row, bar);
+}
+
+// A ragged batch with several frame shapes in ONE launch: every shape keeps its own geometry
+// and resize mode (a CTA looks its shape up from its block index), so a batch of real camera
+// or dataset frames costs one launch instead of one per shape.
+constexpr int kMixedMaxShapes = 32;
+struct MixedParams {
+  int num_shapes;
+  int first_cta[kMixedMaxShapes + 1];  // CTAs of shape s: [first_cta[s], first_cta[s + 1])
+  int first_img[kMixedMaxShapes];      // its frames: frame[first_img[s] ...]
+  int mode[kMixedMaxShapes];
+  PreParams p[kMixedMaxShapes];
+  const uint8_t* frame[kRaggedMax];
+  int out_index[kRaggedMax];
+};
+
+__global__ void __launch_bounds__(kPreThreads) letterbox_mixed_kernel(const __grid_constant__ MixedParams mp) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(16) float lut[256 * kPreLutRep];
+  __shared__ RowPlan plan[kPreMaxRows];
+  __shared__ int seg_row[2 * kPreMaxRows];
+  __shared__ __align__(8) uint64_t bar;
+  int s = 0;
+  while (s + 1 < mp.num_shapes && (int)blockIdx.x >= mp.first_cta[s + 1]) ++s;
+  const PreParams& p = mp.p[s];
+  const int local = (int)blockIdx.x - mp.first_cta[s];
+  const int img = mp.first_img[s] + local / p.groups;
+  const int y_begin = (local % p.groups) * p.rows_per_cta;
+  const uint8_t* frame = mp.frame[img];
+  const int out_img = mp.out_index[img];
+  switch (mp.mode[s]) {  // uniform over the CTA
+    case kResizeCopy: letterbox_body<false, kResizeCopy>(p, frame, out_img, y_begin, smem, lut, plan, seg_row, bar); break;
+    case kResizeBox2: letterbox_body<false, kResizeBox2>(p, frame, out_img, y_begin, smem, lut, plan, seg_row, bar); break;
+    case kResizeGather: letterbox_body<false, kResizeGather>(p, frame, out_img, y_begin, smem, lut, plan, seg_row, bar); break;
+    default: letterbox_body<false, kResizeLinear>(p, frame, out_img, y_begin, smem, lut, plan, seg_row, bar); break;
+  }
+}
+
 // Distinct source rows the busiest CTA has to stage when each CTA owns `rows` output rows.
 static int max_distinct_rows(int mode, int rows, const ia_letterbox_geom& g, double sc_y) {
   int worst = 1;
@@ -417,6 +461,42 @@ static int launch_letterbox_ragged(const ia_frame_desc* frames, int n, int targe
   for (int i = 0; i < n; ++i) {
     IA_RETURN_IF(!frames[i].data_dev || frames[i].h < 1 || frames[i].w < 1, IA_ERR_INVALID_ARGUMENT);
     by_shape[std::make_pair(frames[i].h, frames[i].w)].push_back(i);
+  }
+  if (by_shape.size() > 1 && by_shape.size() <= (size_t)kMixedMaxShapes && n <= kRaggedMax) {
+    // several shapes, one launch: per-shape geometry and frame pointers in the kernel parameters
+    MixedParams mp;
+    mp.num_shapes = 0;
+    size_t smem_max = 0;
+    long long ctas = 0;
+    int images = 0;
+    for (const auto& kv : by_shape) {
+      const int s = mp.num_shapes++;
+      PreParams& p = mp.p[s];
+      size_t smem;
+      int rc = plan_letterbox(kv.first.first, kv.first.second, target, p, mp.mode[s], smem);
+      if (rc != IA_OK) return rc;
+      p.frames = nullptr;
+      p.out = out;
+      p.divisor = divisor;
+      p.pad_rgb = pad_rgb;
+      p.n = (int)kv.second.size();
+      smem_max = smem > smem_max ? smem : smem_max;
+      mp.first_cta[s] = (int)ctas;
+      mp.first_img[s] = images;
+      for (int i : kv.second) {
+        mp.frame[images] = frames[i].data_dev;
+        mp.out_index[images] = i;
+        ++images;
+      }
+      ctas += (long long)p.groups * p.n;
+      IA_RETURN_IF(ctas > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
+    }
+    mp.first_cta[mp.num_shapes] = (int)ctas;
+    cudaError_t e = cudaFuncSetAttribute(letterbox_mixed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem_max);
+    if (e != cudaSuccess) return (int)e;
+    letterbox_mixed_kernel<<<(unsigned)ctas, kPreThreads, smem_max, stream>>>(mp);
+    return launch_status();
   }
   for (const auto& kv : by_shape) {
     PreParams p;

@@ -39,6 +39,23 @@ def test_preprocess_ragged_many_of_one_shape(D):
         assert np.array_equal(out[i : i + 1], want)
 
 
+def test_preprocess_ragged_launch_paths(D):
+    """Up to 32 shapes and 256 frames go out as one launch (geometry per shape in the kernel
+    parameters); more shapes, or more frames, fall back to one launch per shape.  Same pixels."""
+    rng = np.random.default_rng(5)
+    shapes = [(int(rng.integers(20, 90)), int(rng.integers(20, 90))) for _ in range(40)]
+    frames = [synth.frames(1, h, w, seed=300 + i)[0] for i, (h, w) in enumerate(shapes)]
+    dev = [torch.from_numpy(f).cuda() for f in frames]
+    many = D.preprocess_ragged_cuda(dev, target=64).cpu().numpy()  # 40 shapes: per-shape launches
+    few = D.preprocess_ragged_cuda(dev[:30], target=64).cpu().numpy()  # 30 shapes: one launch
+    assert np.array_equal(many[:30], few)
+    for i in (0, 7, 29, 39):
+        want, *_ = O.yolo_preprocess(frames[i], target=64)
+        assert np.array_equal(many[i : i + 1], want), shapes[i]
+    big = D.preprocess_ragged_cuda([dev[i % 5] for i in range(260)], target=64).cpu().numpy()  # > 256 frames
+    assert np.array_equal(big[255:260], few[[0, 1, 2, 3, 4]])
+
+
 def test_crop_ragged(D):
     shapes = [(480, 640), (1080, 1920), (427, 640), (500, 375), (720, 1280), (333, 500)]
     frames = [synth.frames(1, h, w, seed=300 + i)[0] for i, (h, w) in enumerate(shapes)]
