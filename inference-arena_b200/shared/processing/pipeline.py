@@ -124,6 +124,43 @@ class GraphedPipeline:
         return self.out
 
 
+class RaggedPipeline:
+    """The chain for a batch of requests as a service receives them: frames of different
+    sizes, given as uint8 [H_i,W_i,3] CUDA tensors or as baseline JPEG files (``bytes``, decoded
+    on the device).  One launch each for K1 (up to 32 shapes), K2, K3 and K4; the detections of
+    image i are in its own letterbox space, exactly as the reference's per-request loop
+    (monolithic/app/inference.py:153-193) produces them."""
+
+    def __init__(self, device: torch.device | str = "cuda", anchors: int = 25200, classes: int = 80,
+                 conf: float = 0.25, iou: float = 0.45, target: int = 640, crop_size: int = 224,
+                 max_det: int = 32, max_candidates: int = 4096, rois_per_image: int = 8) -> None:
+        self.device = torch.device(device)
+        self.anchors, self.classes, self.conf, self.iou = anchors, classes, conf, iou
+        self.target, self.crop_size, self.max_det = target, crop_size, max_det
+        self.max_candidates = min(max_candidates, anchors)
+        self.rois_per_image = rois_per_image
+        self._decoder = None
+        self._workspace = None
+
+    def run(self, frames, head: torch.Tensor) -> PipelineOutput:
+        if frames and isinstance(frames[0], (bytes, bytearray, memoryview)):
+            if self._decoder is None:
+                from .jpeg import JpegDecoder
+                self._decoder = JpegDecoder(self.device)
+            frames = self._decoder.decode([bytes(f) for f in frames]).frames
+        n = len(frames)
+        need = D.lib().ia_decode_nms_workspace_bytes(n, self.anchors, self.max_candidates)
+        if self._workspace is None or self._workspace.numel() < need:
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
+        tensor = D.preprocess_ragged_cuda(frames, self.target)
+        dets, keep, count, status = D.decode_nms_cuda(
+            head, self.conf, self.iou, max_candidates=self.max_candidates, max_det=self.max_det,
+            workspace=self._workspace)
+        crops, offsets, rois = D.crop_ragged_cuda(frames, dets, count, self.target, self.crop_size,
+                                                  roi_capacity=n * self.rois_per_image)
+        return PipelineOutput(tensor, dets, keep, count, status, crops, offsets, rois)
+
+
 class HostTicket:
     """Handle of one submitted batch: ``wait()`` blocks until its outputs are in host memory
     and returns them (views into the pipeline's pinned result set; valid until the

@@ -134,3 +134,30 @@ def test_device_pipeline_overlapped_streams():
         out = pipe.run(torch.from_numpy(frames).cuda(), torch.from_numpy(heads).cuda(), overlap=True)
     torch.cuda.synchronize()
     _check_device(out, _oracle(frames, heads))
+
+
+def test_ragged_pipeline_from_mixed_jpeg_files():
+    """A service-like batch: JPEG files of different sizes and samplings -> device decode ->
+    K1 (one launch for all shapes) -> K2+K3 -> K4, against the oracle applied per request."""
+    pytest.importorskip("cv2")
+    from shared.processing.pipeline import RaggedPipeline
+    from workloads import jpeg_cases as W
+
+    shapes = [(480, 640), (427, 640), (375, 500), (640, 480), (333, 500), (480, 640), (612, 612), (240, 320)]
+    files = [W.encode(W.photo(h, w, seed=90 + i), 88, W.SAMPLINGS[i % 3]) for i, (h, w) in enumerate(shapes)]
+    # cv2.imdecode is the call load_image_from_bytes makes; oracle/jpeg.py is pinned equal to it
+    # (tests/test_oracle_jpeg.py) but is a pure-Python loop, too slow for frames of this size
+    frames = [W.reference_decode(f) for f in files]
+    heads = synth.head_v5(len(files), seed=91)
+    pipe = RaggedPipeline("cuda")
+    for given in (files, [torch.from_numpy(f).cuda() for f in frames]):
+        out = pipe.run(given, torch.from_numpy(heads).cuda())
+        torch.cuda.synchronize()
+        offs = out.roi_offsets.cpu().numpy()
+        for i, (frame, head) in enumerate(zip(frames, heads)):
+            tensor, dets, keep, _, crops = O.run_image(frame, head, 0.25, 0.45)
+            k = int(out.count[i])
+            assert int(out.status[i]) == 0 and out.keep[i, :k].cpu().tolist() == keep
+            assert np.array_equal(out.tensor[i : i + 1].cpu().numpy(), tensor), shapes[i]
+            assert np.array_equal(out.dets[i, :k].cpu().numpy(), dets)
+            assert np.array_equal(out.crops[offs[i] : offs[i + 1]].cpu().numpy(), crops), shapes[i]
