@@ -11,7 +11,9 @@ h, w = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (1080, 192
 batch_n = int(sys.argv[3]) if len(sys.argv) > 3 else 64
 q = int(sys.argv[4]) if len(sys.argv) > 4 else 90
 reps = int(sys.argv[5]) if len(sys.argv) > 5 else 20
-blobs = [W.encode(W.photo(h, w, seed=i), q, "420") for i in range(min(batch_n, 8))]
+samp = sys.argv[6] if len(sys.argv) > 6 else "420"
+blobs = [(W.encode(W.photo(h, w, seed=i)[..., 0], q) if samp == "gray" else W.encode(W.photo(h, w, seed=i), q, samp))
+         for i in range(min(batch_n, 8))]
 blobs = [blobs[i % len(blobs)] for i in range(batch_n)]
 kb = sum(len(b) for b in blobs) / batch_n / 1024
 batch = M.decode_jpeg_batch_cuda(blobs); torch.cuda.synchronize()
