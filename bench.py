@@ -375,6 +375,15 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
             "cv2_imdecode_one_core_ms_per_image": cpu_ms,
             "cv2_imdecode_all_cores_images_per_s": cpu_all, "host_cores": cores}
         del batch, last
+        # the same frames at quality 75 (files of the size photographs usually have)
+        files75 = [W.encode(W.photo(1080, 1920, seed=i), 75, "420") for i in range(8)]
+        batch = J.decode_jpeg_batch_cuda([files75[i % 8] for i in range(64)], dev)
+        torch.cuda.synchronize(dev)
+        ms75 = time_loop(batch.rerun, max(steps // 4, 10), 3, dev)
+        out["N3_jpeg_decode_64x1080p"]["quality75"] = {
+            "images_per_s": 64 / ms75 * 1e3, "ms": ms75, "file_kb": sum(map(len, files75)) / 8 / 1024,
+            "status_ok": int(batch.status.sum().item()) == 0}
+        del batch
     except ImportError as e:  # no encoder for the synthetic files on this box
         out["N3_jpeg_decode_64x1080p"] = {"skipped": str(e)}
     return out
