@@ -176,3 +176,27 @@ def test_truncated_stream_is_flagged(M):
     batch = M.decode_jpeg_batch_cuda([data[: len(data) * 2 // 3]])
     torch.cuda.synchronize()
     assert batch.status.cpu().tolist() == [1]
+
+
+def test_two_decoders_on_two_streams(M):
+    """Two JpegDecoder objects, each on its own stream, launched back to back so that their
+    kernels (and the Huffman kernel's look-back chains) overlap on the device."""
+    a = [W.encode(W.photo(300, 400, seed=40 + i), 90, "420") for i in range(12)]
+    b = [W.encode(W.photo(200, 520, seed=60 + i), 60, "444", restart=5) for i in range(12)]
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    d1, d2 = M.JpegDecoder("cuda"), M.JpegDecoder("cuda")
+    outs = []
+    for _ in range(3):
+        with torch.cuda.stream(s1):
+            o1 = d1.decode(a)
+        with torch.cuda.stream(s2):
+            o2 = d2.decode(b)
+        outs.append((o1, o2))
+    torch.cuda.synchronize()
+    for o1, o2 in outs[-1:]:
+        assert o1.status.cpu().tolist() == [0] * 12 and o2.status.cpu().tolist() == [0] * 12
+        for f, data in zip(o1.frames + o2.frames, a + b):
+            assert np.array_equal(f.cpu().numpy(), W.reference_decode(data))
+    for o1, o2 in outs[:-1]:  # frames of earlier calls are the callers' own tensors: still intact
+        assert np.array_equal(o1.frames[0].cpu().numpy(), W.reference_decode(a[0]))
+        assert np.array_equal(o2.frames[5].cpu().numpy(), W.reference_decode(b[5]))
