@@ -9,7 +9,7 @@
 //                             128 bytes, one per thread), self-synchronising decode inside
 //                             the CTA, chunks chained through a ticketed look-back
 //   I  idct_kernel            one thread per 8x8 block, jidctint.c "islow"
-//   C  colour_kernel          four pixels per thread: fancy upsampling, YCbCr->RGB, orientation
+//   C  colour_kernel          eight pixels per thread: fancy upsampling, YCbCr->RGB, orientation
 #pragma once
 
 #include "ia_common.cuh"
@@ -745,7 +745,7 @@ __device__ __forceinline__ int chroma_sample(const uint8_t* __restrict__ plane, 
   return plane[(size_t)(y / vexp) * pitch + x / hexp];
 }
 
-constexpr int kColourPixels = 4;  // consecutive pixels of a row per thread
+constexpr int kColourPixels = 8;  // consecutive pixels of a row per thread
 
 __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restrict__ jobs) {
   const ia_jpeg_job& J = jobs[blockIdx.z];
@@ -755,9 +755,9 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
   const uint8_t* __restrict__ yrow = J.plane_dev[0] + (size_t)y * J.comp_pitch[0];
   const int ncomp = J.ncomp, orientation = J.orientation;
   const int count = min(kColourPixels, W - x0);
-  // chroma of the four pixels.  Interior groups of the common layouts (4:2:0, 4:2:2, 4:4:4) use
-  // four bytes per chroma row; everything else (image borders, other factors, tiny planes)
-  // goes pixel by pixel through chroma_sample.
+  // chroma of the eight pixels.  Interior groups of the common layouts (4:2:0, 4:2:2) read one
+  // aligned word + two bytes per chroma row; everything else (image borders, other factors,
+  // tiny planes) goes pixel by pixel through chroma_sample.
   int chroma[2][kColourPixels];
   if (ncomp == 3) {
 #pragma unroll
@@ -765,25 +765,33 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
       const int hexp = J.hexp[k + 1], vexp = J.vexp[k + 1], dw = J.comp_w[k + 1], dh = J.comp_h[k + 1];
       const int pitch = J.comp_pitch[k + 1];
       const uint8_t* __restrict__ plane = J.plane_dev[k + 1];
-      const int xc = x0 >> 1;
-      if (hexp == 2 && vexp <= 2 && count == kColourPixels && xc >= 1 && xc + 2 <= dw - 1 && dw > 2) {
+      const int xc = x0 >> 1;  // a multiple of 4: the four samples xc..xc+3 are one aligned word
+      if (hexp == 2 && vexp <= 2 && count == kColourPixels && xc >= 1 && xc + 4 <= dw - 1 && dw > 2) {
         const int yc = vexp == 2 ? y >> 1 : y;
         int yo = yc;
         if (vexp == 2) {
           yo = (y & 1) ? yc + 1 : yc - 1;
           yo = yo < 0 ? 0 : (yo > dh - 1 ? dh - 1 : yo);
         }
-        const uint8_t* r0 = plane + (size_t)yc * pitch + xc - 1;
-        const uint8_t* r1 = plane + (size_t)yo * pitch + xc - 1;
-        int cs[4];  // h2v2: 3 * near row + far row ("colsum"); h2v1: the sample itself
+        const uint8_t* r0 = plane + (size_t)yc * pitch + xc;
+        const uint8_t* r1 = plane + (size_t)yo * pitch + xc;
+        const uint32_t w0 = *reinterpret_cast<const uint32_t*>(r0), w1 = *reinterpret_cast<const uint32_t*>(r1);
+        int near_[6], far_[6];  // samples xc-1 .. xc+4 of the near and the far chroma row
+        near_[0] = r0[-1], near_[5] = r0[4], far_[0] = r1[-1], far_[5] = r1[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) cs[i] = vexp == 2 ? 3 * r0[i] + r1[i] : r0[i];
-        if (vexp == 2) {
-          chroma[k][0] = (3 * cs[1] + cs[0] + 8) >> 4, chroma[k][1] = (3 * cs[1] + cs[2] + 7) >> 4;
-          chroma[k][2] = (3 * cs[2] + cs[1] + 8) >> 4, chroma[k][3] = (3 * cs[2] + cs[3] + 7) >> 4;
-        } else {
-          chroma[k][0] = (3 * cs[1] + cs[0] + 1) >> 2, chroma[k][1] = (3 * cs[1] + cs[2] + 2) >> 2;
-          chroma[k][2] = (3 * cs[2] + cs[1] + 1) >> 2, chroma[k][3] = (3 * cs[2] + cs[3] + 2) >> 2;
+        for (int i = 0; i < 4; ++i) near_[i + 1] = (w0 >> (8 * i)) & 255u, far_[i + 1] = (w1 >> (8 * i)) & 255u;
+        int cs[6];  // h2v2: 3 * near row + far row ("colsum"); h2v1: the sample itself
+#pragma unroll
+        for (int i = 0; i < 6; ++i) cs[i] = vexp == 2 ? 3 * near_[i] + far_[i] : near_[i];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (vexp == 2) {
+            chroma[k][2 * i] = (3 * cs[i + 1] + cs[i] + 8) >> 4;
+            chroma[k][2 * i + 1] = (3 * cs[i + 1] + cs[i + 2] + 7) >> 4;
+          } else {
+            chroma[k][2 * i] = (3 * cs[i + 1] + cs[i] + 1) >> 2;
+            chroma[k][2 * i + 1] = (3 * cs[i + 1] + cs[i + 2] + 2) >> 2;
+          }
         }
       } else if (hexp == 1 && vexp == 1) {
 #pragma unroll
@@ -796,10 +804,18 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
     }
   }
   uint8_t rgb[kColourPixels * 3];
+  int luma[kColourPixels];
+  if (count == kColourPixels) {  // x0 is a multiple of 8 and so is the pitch: one aligned 64-bit load
+    const uint2 yv = *reinterpret_cast<const uint2*>(yrow + x0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) luma[i] = (yv.x >> (8 * i)) & 255u, luma[i + 4] = (yv.y >> (8 * i)) & 255u;
+  } else {
+#pragma unroll
+    for (int i = 0; i < kColourPixels; ++i) luma[i] = yrow[min(x0 + i, W - 1)];
+  }
 #pragma unroll
   for (int i = 0; i < kColourPixels; ++i) {
-    const int x = min(x0 + i, W - 1);
-    const int yy = yrow[x];
+    const int yy = luma[i];
     int r, g, b;
     if (ncomp == 1) {
       r = g = b = yy;
@@ -821,7 +837,7 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
     if (count == kColourPixels && ((uintptr_t)o & 3) == 0) {
       uint32_t* o32 = reinterpret_cast<uint32_t*>(o);
 #pragma unroll
-      for (int k = 0; k < 3; ++k)
+      for (int k = 0; k < kColourPixels * 3 / 4; ++k)
         o32[k] = rgb[4 * k] | (rgb[4 * k + 1] << 8) | (rgb[4 * k + 2] << 16) | ((uint32_t)rgb[4 * k + 3] << 24);
     } else {
       for (int k = 0; k < count * 3; ++k) o[k] = rgb[k];
