@@ -766,7 +766,10 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
       const int pitch = J.comp_pitch[k + 1];
       const uint8_t* __restrict__ plane = J.plane_dev[k + 1];
       const int xc = x0 >> 1;  // a multiple of 4: the four samples xc..xc+3 are one aligned word
-      if (hexp == 2 && vexp <= 2 && count == kColourPixels && xc >= 1 && xc + 4 <= dw - 1 && dw > 2) {
+      if (hexp == 2 && vexp <= 2 && count == kColourPixels && xc + 3 <= dw - 1 && dw > 2) {
+        // the first / last group of a row has no left / right neighbour sample: jdsample.c's
+        // edge formulas for those two pixels, everything else as in the interior
+        const bool has_left = xc >= 1, has_right = xc + 4 <= dw - 1;
         const int yc = vexp == 2 ? y >> 1 : y;
         int yo = yc;
         if (vexp == 2) {
@@ -777,7 +780,8 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
         const uint8_t* r1 = plane + (size_t)yo * pitch + xc;
         const uint32_t w0 = *reinterpret_cast<const uint32_t*>(r0), w1 = *reinterpret_cast<const uint32_t*>(r1);
         int near_[6], far_[6];  // samples xc-1 .. xc+4 of the near and the far chroma row
-        near_[0] = r0[-1], near_[5] = r0[4], far_[0] = r1[-1], far_[5] = r1[4];
+        near_[0] = r0[has_left ? -1 : 0], near_[5] = r0[has_right ? 4 : 3];
+        far_[0] = r1[has_left ? -1 : 0], far_[5] = r1[has_right ? 4 : 3];
 #pragma unroll
         for (int i = 0; i < 4; ++i) near_[i + 1] = (w0 >> (8 * i)) & 255u, far_[i + 1] = (w1 >> (8 * i)) & 255u;
         int cs[6];  // h2v2: 3 * near row + far row ("colsum"); h2v1: the sample itself
@@ -793,6 +797,8 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
             chroma[k][2 * i + 1] = (3 * cs[i + 1] + cs[i + 2] + 2) >> 2;
           }
         }
+        if (!has_left) chroma[k][0] = vexp == 2 ? (4 * cs[1] + 8) >> 4 : cs[1];
+        if (!has_right) chroma[k][7] = vexp == 2 ? (4 * cs[4] + 7) >> 4 : cs[4];
       } else if (hexp == 1 && vexp == 1) {
 #pragma unroll
         for (int i = 0; i < kColourPixels; ++i) chroma[k][i] = plane[(size_t)y * pitch + min(x0 + i, W - 1)];
@@ -840,11 +846,15 @@ __global__ void __launch_bounds__(256) colour_kernel(const ia_jpeg_job* __restri
       for (int k = 0; k < kColourPixels * 3 / 4; ++k)
         o32[k] = rgb[4 * k] | (rgb[4 * k + 1] << 8) | (rgb[4 * k + 2] << 16) | ((uint32_t)rgb[4 * k + 3] << 24);
     } else {
-      for (int k = 0; k < count * 3; ++k) o[k] = rgb[k];
+#pragma unroll
+      for (int k = 0; k < kColourPixels * 3; ++k)  // constant indices: rgb[] stays in registers
+        if (k < count * 3) o[k] = rgb[k];
     }
     return;
   }
-  for (int i = 0; i < count; ++i) {  // OpenCV's ExifTransform
+#pragma unroll
+  for (int i = 0; i < kColourPixels; ++i) {  // OpenCV's ExifTransform
+    if (i >= count) break;
     const int x = x0 + i;
     int ox = x, oy = y;
     switch (orientation) {
