@@ -179,19 +179,26 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
   cut_at(end, r0, keep_mask, bnd_mask);
   uint32_t total;
   const uint32_t excl = cta_scan_packed((uint32_t)__popc(keep_mask) | ((uint32_t)__popc(bnd_mask) << 16), s_warp, total);
-  uint32_t pos = rec[0] + (excl & 0xffffu);
+  // compact the tile in shared memory first, then write it out with consecutive lanes on
+  // consecutive bytes (a thread's own run of ~16 bytes would cost a sector per lane and store)
+  __shared__ uint8_t s_tile[kTileBytes];
+  const uint32_t tile_base = rec[0];
+  uint32_t local = excl & 0xffffu;
   uint32_t bpos = rec[1] + (excl >> 16);
-  uint8_t* __restrict__ clean = J.clean_dev;
   uint32_t* __restrict__ seg = J.segment_dev;
   const uint32_t seg_cap = (uint32_t)J.num_segments;
 #pragma unroll
   for (int k = 0; k < kUnstuffPerThread; ++k) {
-    if (keep_mask >> k & 1u) clean[pos++] = b[k + 1];
+    if (keep_mask >> k & 1u) s_tile[local++] = b[k + 1];
     if (bnd_mask >> k & 1u) {
-      if (bpos < seg_cap) seg[2 + bpos] = pos;  // the next segment starts at this clean byte
+      if (bpos < seg_cap) seg[2 + bpos] = tile_base + local;  // the next segment starts at this clean byte
       ++bpos;
     }
   }
+  __syncthreads();
+  uint8_t* __restrict__ clean = J.clean_dev + tile_base;
+  const uint32_t kept = total & 0xffffu;
+  for (uint32_t i = threadIdx.x; i < kept; i += kUnstuffThreads) clean[i] = s_tile[i];
 }
 
 // ================================================================================ Huffman
