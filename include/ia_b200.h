@@ -294,7 +294,8 @@ typedef struct ia_jpeg_job {
   uint8_t dc_counts[4][16], dc_vals[4][16];
   uint8_t ac_counts[4][16], ac_vals[4][256];
   /* --- filled by ia_jpeg_plan (device pointers) --- */
-  const uint8_t* file_dev; /* the whole file */
+  const uint8_t* file_dev; /* the whole file; read in aligned 16-byte units, so the bytes up to the next
+                              16-byte boundary after its end must be readable (any cudaMalloc'ed buffer is) */
   uint8_t* clean_dev;      /* entropy-coded bytes without stuffing / RST markers */
   uint32_t* segment_dev;   /* [0] clean bytes, [1] restart boundaries found, [2..] their clean byte offsets */
   int16_t* coef_dev;       /* [total_blocks, 64] natural order, DC absolute, not dequantised */

@@ -41,13 +41,34 @@ __host__ __device__ inline uint32_t chunk_capacity(const ia_jpeg_job& j) {
 // ================================================================================ unstuff
 // Classify the 16 bytes [r0, r0+16) of the scan: which survive, which end a restart marker,
 // and the first position that starts any other marker (the end of the scan).
-__device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n, uint32_t r0, uint8_t (&b)[18],
-                                         uint32_t& keep_mask, uint32_t& bnd_mask, uint32_t& my_end) {
+//
+// Threads are laid out over the 16-byte aligned stream that contains the scan (v0 = this
+// thread's offset from the aligned address at or below the scan start), so the 16 bytes are one
+// 128-bit load; the byte before and the byte after come from the neighbouring lanes.  r0 (out)
+// is the scan-relative position of the thread's first byte and may be negative for the very
+// first thread; bytes outside [0, n) are never kept (before the scan they read as 0, after it
+// as an EOI marker).
+__device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n, uint32_t v0, uint8_t (&b)[18],
+                                         uint32_t& keep_mask, uint32_t& bnd_mask, uint32_t& my_end, long long& r_first) {
+  const uint32_t a = (uint32_t)((uintptr_t)src & 15);
+  const uint8_t* __restrict__ base = src - a;
+  const uint32_t nv = n + a;  // length of the aligned stream that still belongs to the scan
+  auto fix = [&](uint32_t v, uint32_t raw) -> uint8_t {  // byte at aligned offset v
+    return v < a ? (uint8_t)0 : (v < nv ? (uint8_t)raw : (uint8_t)0xD9);
+  };
+  uint4 q = make_uint4(0, 0, 0, 0);
+  if (v0 < nv) q = __ldg(reinterpret_cast<const uint4*>(base + v0));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-  for (int k = 0; k < kUnstuffPerThread + 2; ++k) {
-    const uint32_t idx = r0 + k - 1;  // b[k] = byte r0 - 1 + k; the byte before the scan reads as 0
-    b[k] = (r0 + k == 0) ? 0 : (idx < n ? __ldg(src + idx) : 0xD9);
-  }
+  for (int k = 0; k < kUnstuffPerThread; ++k) b[k + 1] = fix(v0 + k, (w[k >> 2] >> (8 * (k & 3))) & 255u);
+  const int lane = threadIdx.x & 31;
+  uint32_t prev = __shfl_up_sync(0xffffffffu, (uint32_t)b[kUnstuffPerThread], 1);
+  uint32_t next = __shfl_down_sync(0xffffffffu, (uint32_t)b[1], 1);
+  if (lane == 0) prev = v0 == 0 ? 0u : fix(v0 - 1, (v0 - 1 < nv) ? __ldg(base + v0 - 1) : 0u);
+  if (lane == 31) next = fix(v0 + 16, (v0 + 16 < nv) ? __ldg(base + v0 + 16) : 0u);
+  b[0] = (uint8_t)prev, b[kUnstuffPerThread + 1] = (uint8_t)next;
+  r_first = (long long)v0 - (long long)a;
+  const uint32_t r0 = v0 - a;  // wraps for bytes before the scan: those fail r < n below
   keep_mask = 0, bnd_mask = 0, my_end = 0xffffffffu;
 #pragma unroll
   for (int k = 0; k < kUnstuffPerThread; ++k) {
@@ -66,10 +87,10 @@ __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32
   }
 }
 
-__device__ __forceinline__ void cut_at(uint32_t end, uint32_t r0, uint32_t& keep_mask, uint32_t& bnd_mask) {
-  if (end < r0 + kUnstuffPerThread) {
-    const uint32_t valid = end > r0 ? end - r0 : 0;
-    const uint32_t m = (1u << valid) - 1u;  // valid < 16
+__device__ __forceinline__ void cut_at(uint32_t end, long long r_first, uint32_t& keep_mask, uint32_t& bnd_mask) {
+  if ((long long)end < r_first + kUnstuffPerThread) {
+    const long long valid = (long long)end > r_first ? (long long)end - r_first : 0;  // < 16
+    const uint32_t m = (1u << (int)valid) - 1u;
     keep_mask &= m, bnd_mask &= m;
   }
 }
@@ -111,11 +132,12 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_count_kernel(const ia
   const uint32_t r0 = tile * kTileBytes + threadIdx.x * kUnstuffPerThread;
   uint8_t b[18];
   uint32_t keep_mask, bnd_mask, my_end;
-  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end);
+  long long r_first;
+  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end, r_first);
   if (my_end != 0xffffffffu) atomicMin(&s_end, my_end);
   __syncthreads();
   const uint32_t end = s_end;
-  cut_at(end, r0, keep_mask, bnd_mask);
+  cut_at(end, r_first, keep_mask, bnd_mask);
   uint32_t total;
   cta_scan_packed((uint32_t)__popc(keep_mask) | ((uint32_t)__popc(bnd_mask) << 16), s_warp, total);
   if (threadIdx.x == 0) {
@@ -175,8 +197,9 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
   const uint32_t r0 = tile * kTileBytes + threadIdx.x * kUnstuffPerThread;
   uint8_t b[18];
   uint32_t keep_mask, bnd_mask, my_end;
-  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end);
-  cut_at(end, r0, keep_mask, bnd_mask);
+  long long r_first;
+  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end, r_first);
+  cut_at(end, r_first, keep_mask, bnd_mask);
   uint32_t total;
   const uint32_t excl = cta_scan_packed((uint32_t)__popc(keep_mask) | ((uint32_t)__popc(bnd_mask) << 16), s_warp, total);
   // compact the tile in shared memory first, then write it out with consecutive lanes on
