@@ -132,6 +132,19 @@ def test_mixed_batch(M):
             assert np.array_equal(got.cpu().numpy(), W.reference_decode(data))
 
 
+def test_16bit_quantisation_tables_and_comment_segments(M):
+    """Header variants encoders rarely emit: 16-bit DQT entries, a COM segment full of 0xFF
+    bytes and marker look-alikes in front of the scan."""
+    data = W.encode(W.photo(120, 200, seed=12), 40, "420", restart=3)
+    wide = W.with_16bit_quant_tables(data)
+    junk = bytes([0xFF, 0xD8, 0xFF, 0xDA, 0xFF, 0x00, 0xFF, 0xD9] * 9)
+    noisy = wide[:2] + b"\xff\xfe" + (len(junk) + 2).to_bytes(2, "big") + junk + wide[2:]
+    sof = noisy.index(b"\xff\xc0", 2 + 4 + len(junk))
+    extended = noisy[:sof] + b"\xff\xc1" + noisy[sof + 2:]  # SOF1: extended sequential, same decoding
+    for blob in (wide, noisy, extended):
+        assert np.array_equal(M.load_jpeg_from_bytes(blob), W.reference_decode(blob))
+
+
 def test_errors(M):
     with pytest.raises(M.UnsupportedJpeg):
         M.decode_jpeg_batch_cuda([W.encode(W.photo(16, 16, 1), 90, "420", progressive=True)])

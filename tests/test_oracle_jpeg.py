@@ -53,6 +53,20 @@ def test_reference_fixtures(golden):
         assert np.array_equal(got, golden[f"jpeg{i}_rgb"]), case
 
 
+def test_16bit_quantisation_tables(jpeg_mod):
+    """DQT with Pq = 1: same pixels from cv2, the oracle and the same tables from the host parser."""
+    data = W.encode(W.photo(40, 56, seed=1), 60, "420", optimize=True)
+    wide = W.with_16bit_quant_tables(data)
+    assert len(wide) == len(data) + 128
+    want = W.reference_decode(wide)
+    assert np.array_equal(want, W.reference_decode(data))
+    assert np.array_equal(J.load_image_from_bytes(wide), want)
+    a, b = jpeg_mod.parse_jpeg(data), jpeg_mod.parse_jpeg(wide)
+    for c in range(3):
+        assert list(a.quant[c]) == list(b.quant[c])
+    assert b.scan_offset == a.scan_offset + 128
+
+
 def test_rejects():
     with pytest.raises(J.UnsupportedJpeg):
         J.parse(W.encode(W.photo(16, 16, 1), 90, "420", progressive=True))

@@ -65,3 +65,36 @@ def reference_decode(jpeg: bytes) -> np.ndarray:
     if bgr is None:
         raise ValueError("Failed to decode image from bytes")
     return cv2.cvtColor(bgr, cv2.COLOR_BGR2RGB)
+
+
+def with_16bit_quant_tables(jpeg: bytes) -> bytes:
+    """Rewrite every 8-bit DQT table of the header as a 16-bit one (Pq = 1) with the same values:
+    legal, rarely produced by encoders, and a separate branch in every decoder."""
+    out = bytearray(jpeg[:2])
+    i = 2
+    while True:
+        assert jpeg[i] == 0xFF
+        m = jpeg[i + 1]
+        length = (jpeg[i + 2] << 8) | jpeg[i + 3]
+        seg = jpeg[i + 4:i + 2 + length]
+        if m == 0xDB:
+            body = bytearray()
+            k = 0
+            while k < len(seg):
+                pq, tq = seg[k] >> 4, seg[k] & 15
+                k += 1
+                if pq:
+                    body += bytes([seg[k - 1]]) + seg[k:k + 128]
+                    k += 128
+                else:
+                    body.append(0x10 | tq)
+                    for v in seg[k:k + 64]:
+                        body += bytes([0, v])
+                    k += 64
+            out += b"\xff\xdb" + struct.pack(">H", len(body) + 2) + body
+        else:
+            out += jpeg[i:i + 2 + length]
+        i += 2 + length
+        if m == 0xDA:
+            break
+    return bytes(out) + jpeg[i:]
