@@ -141,7 +141,11 @@ def test_16bit_quantisation_tables_and_comment_segments(M):
     noisy = wide[:2] + b"\xff\xfe" + (len(junk) + 2).to_bytes(2, "big") + junk + wide[2:]
     sof = noisy.index(b"\xff\xc0", 2 + 4 + len(junk))
     extended = noisy[:sof] + b"\xff\xc1" + noisy[sof + 2:]  # SOF1: extended sequential, same decoding
-    for blob in (wide, noisy, extended):
+    import re
+    start = J.parse(data)["scan_start"]  # fill bytes (extra 0xFF) in front of every restart marker
+    filled = data[:start] + re.sub(rb"\xff([\xd0-\xd7])", lambda m: b"\xff\xff\xff" + m.group(1), data[start:])
+    assert len(filled) > len(data)
+    for blob in (wide, noisy, extended, filled):
         assert np.array_equal(M.load_jpeg_from_bytes(blob), W.reference_decode(blob))
 
 
