@@ -70,7 +70,7 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
   bool have_qt[4] = {false, false, false, false}, have_dc[4] = {false, false, false, false},
        have_ac[4] = {false, false, false, false};
   int tq[IA_JPEG_MAX_COMPONENTS] = {0, 0, 0}, comp_id[IA_JPEG_MAX_COMPONENTS] = {0, 0, 0};
-  bool have_sof = false, saw_exif = false;
+  bool have_sof = false, saw_exif = false, saw_jfif = false;
   int adobe_transform = -1;
   job->orientation = 1;
   size_t i = 2;
@@ -143,6 +143,8 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
       job->orientation = exif_orientation(seg, len);
     } else if (m == 0xEE && len >= 12 && memcmp(seg, "Adobe", 5) == 0) {
       adobe_transform = seg[11];
+    } else if (m == 0xE0 && len >= 5 && memcmp(seg, "JFIF\0", 5) == 0) {
+      saw_jfif = true;
     } else if (m == 0xDA) {
       IA_RETURN_IF(!have_sof || len < 1, IA_ERR_INVALID_ARGUMENT);
       const int ns = seg[0];
@@ -161,7 +163,12 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
     i += L;
   }
   IA_RETURN_IF(job->width < 1 || job->height < 1, IA_ERR_INVALID_ARGUMENT);
-  IA_RETURN_IF(job->ncomp == 3 && adobe_transform == 0, IA_ERR_UNSUPPORTED);  // stored as RGB
+  // libjpeg's guess of the colour space (jdapimin.c default_decompress_parms): JFIF means YCbCr;
+  // else an Adobe marker decides; else the component ids 'R','G','B' mean RGB.  RGB is not decoded here.
+  if (job->ncomp == 3 && !saw_jfif) {
+    const bool ids_rgb = comp_id[0] == 'R' && comp_id[1] == 'G' && comp_id[2] == 'B';
+    IA_RETURN_IF(adobe_transform == 0 || (adobe_transform < 0 && ids_rgb), IA_ERR_UNSUPPORTED);
+  }
   if (job->ncomp == 1) job->h[0] = job->v[0] = 1;  // sampling factors mean nothing for one component
   job->hmax = job->vmax = 1;
   int bpm = 0;

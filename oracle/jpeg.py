@@ -132,6 +132,8 @@ def parse(data: bytes) -> dict:
             info["orientation"] = _exif_orientation(seg)
         elif m == 0xEE and seg[:5] == b"Adobe" and len(seg) >= 12:
             info["adobe_transform"] = seg[11]
+        elif m == 0xE0 and seg[:5] == b"JFIF\x00":
+            info["jfif"] = True
         elif m == 0xDA:  # SOS
             ns = seg[0]
             if "comps" not in info:
@@ -150,8 +152,12 @@ def parse(data: bytes) -> dict:
     nc = len(info["comps"])
     if nc not in (1, 3):
         raise UnsupportedJpeg(f"{nc} components")
-    if nc == 3 and info["adobe_transform"] == 0:
-        raise UnsupportedJpeg("Adobe RGB (no YCbCr transform)")
+    # libjpeg's colour-space guess (jdapimin.c default_decompress_parms): JFIF -> YCbCr; else the
+    # Adobe marker decides; else component ids 'R','G','B' -> RGB
+    if nc == 3 and not info.get("jfif"):
+        ids_rgb = [c["id"] for c in info["comps"]] == [ord("R"), ord("G"), ord("B")]
+        if info["adobe_transform"] == 0 or (info["adobe_transform"] is None and ids_rgb):
+            raise UnsupportedJpeg("stored as RGB (no YCbCr transform)")
     if nc == 1:
         info["comps"][0]["h"] = info["comps"][0]["v"] = 1  # sampling factors mean nothing here
     if info["width"] == 0 or info["height"] == 0:

@@ -67,6 +67,31 @@ def test_16bit_quantisation_tables(jpeg_mod):
     assert b.scan_offset == a.scan_offset + 128
 
 
+def test_colour_space_guess_follows_libjpeg(jpeg_mod):
+    """jdapimin.c default_decompress_parms: without a JFIF or Adobe marker three components with
+    ids 1,2,3 are still YCbCr; ids 'R','G','B' mean stored RGB (cv2 then returns other pixels), which
+    the device decoder refuses instead of converting wrongly."""
+    data = W.encode(W.photo(40, 56, seed=1), 80, "444")
+    assert data[2:4] == b"\xff\xe0"
+    app0 = (data[4] << 8) | data[5]
+    bare = data[:2] + data[4 + app0:]  # no JFIF segment
+    want = W.reference_decode(data)
+    assert np.array_equal(W.reference_decode(bare), want)
+    assert np.array_equal(J.load_image_from_bytes(bare), want)
+    assert jpeg_mod.parse_jpeg(bare).ncomp == 3
+    rgb = bytearray(bare)
+    sof, sos = rgb.index(b"\xff\xc0"), rgb.index(b"\xff\xda")
+    for c, ch in enumerate(b"RGB"):
+        rgb[sof + 10 + 3 * c] = ch
+        rgb[sos + 5 + 2 * c] = ch
+    rgb = bytes(rgb)
+    assert not np.array_equal(W.reference_decode(rgb), want)
+    with pytest.raises(J.UnsupportedJpeg):
+        J.parse(rgb)
+    with pytest.raises(jpeg_mod.UnsupportedJpeg):
+        jpeg_mod.parse_jpeg(rgb)
+
+
 def test_rejects():
     with pytest.raises(J.UnsupportedJpeg):
         J.parse(W.encode(W.photo(16, 16, 1), 90, "420", progressive=True))
