@@ -178,6 +178,8 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
     job->hmax = job->h[c] > job->hmax ? job->h[c] : job->hmax;
     job->vmax = job->v[c] > job->vmax ? job->v[c] : job->vmax;
   }
+  // the colour stage reads the first component at full resolution (every encoder's layout)
+  IA_RETURN_IF(job->h[0] != job->hmax || job->v[0] != job->vmax, IA_ERR_UNSUPPORTED);
   for (int c = 0; c < job->ncomp; ++c) {
     IA_RETURN_IF(job->hmax % job->h[c] || job->vmax % job->v[c], IA_ERR_UNSUPPORTED);
     for (int by = 0; by < job->v[c]; ++by) {

@@ -90,6 +90,11 @@ def test_colour_space_guess_follows_libjpeg(jpeg_mod):
         J.parse(rgb)
     with pytest.raises(jpeg_mod.UnsupportedJpeg):
         jpeg_mod.parse_jpeg(rgb)
+    odd = bytearray(data)  # luma subsampled below chroma: legal, never produced; refused
+    sof = odd.index(b"\xff\xc0")
+    odd[sof + 11], odd[sof + 14], odd[sof + 17] = 0x11, 0x22, 0x22
+    with pytest.raises(jpeg_mod.UnsupportedJpeg):
+        jpeg_mod.parse_jpeg(bytes(odd))
 
 
 def test_rejects():
