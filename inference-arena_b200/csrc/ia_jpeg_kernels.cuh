@@ -27,6 +27,7 @@ constexpr int kUnstuffThreads = 512;
 constexpr int kUnstuffPerThread = 16;
 constexpr uint32_t kTileBytes = kUnstuffThreads * kUnstuffPerThread;
 constexpr int kCleanPad = 64;   // readable zero bytes after the clean stream
+constexpr int kBroadcastEvery = 16;  // huffman_kernel: rounds before the first phase broadcast (then 32, 64 ...)
 constexpr int kChainWords = 16;  // per chunk: tentative and final hand-over records (huffman_kernel)
 constexpr int kTileWords = 4;   // per tile: kept bytes, markers, end position, pad
 
@@ -451,11 +452,15 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
   __shared__ int s_nb[kHuffThreads], s_d0[kHuffThreads], s_d1[kHuffThreads], s_d2[kHuffThreads];
   __shared__ uint8_t s_flag[kHuffThreads];
   __shared__ uint16_t s_task[kHuffThreads];
-  __shared__ int s_wcount[kHuffThreads / 32];
+  __shared__ uint32_t s_votes[kHuffThreads / 32];
+  constexpr int kHistory = 128;  // fronts of the last rounds, indexed by subsequence & 127
+  __shared__ uint32_t s_hist_p[kHistory], s_hist_bz[kHistory];
+  __shared__ int s_hist_t[kHistory];
   __shared__ Agg s_warp_agg[kHuffThreads / 32];
   __shared__ Agg s_carry;
   __shared__ uint32_t s_in_p, s_in_bz, s_ticket;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < kHistory) s_hist_t[tid] = -1;
   if (tid == 0) s_ticket = atomicAdd(ticket_counter, 1u);
   __syncthreads();
   const int image = (int)(s_ticket / (uint32_t)max_chunks), chunk = (int)(s_ticket % (uint32_t)max_chunks);
@@ -491,6 +496,7 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
   // three tasks costs one warp, not sixteen.
   int rounds = 0, tasks = 0;  // diagnostics, published with the chain record
   auto converge = [&](bool first_known) {
+    int local_rounds = 0;  // of this call: the broadcasts below come after 16, 32, 64 ... of them
     for (;;) {
       __syncthreads();  // exits of the previous round are visible
       bool redo = false;
@@ -499,17 +505,83 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
       else if (first_known) np = s_in_p, nbz = s_in_bz;
       if (tid > 0 || first_known) redo = np != s_entry_p[tid] || nbz != s_entry_bz[tid];
       const uint32_t votes = __ballot_sync(0xffffffffu, redo);
-      if (lane == 0) s_wcount[warp] = __popc(votes);
+      if (lane == 0) s_votes[warp] = votes;
       __syncthreads();
-      int base = 0, total = 0;
+      int base = 0, total = 0, front = kHuffThreads;  // front: the first subsequence that repeats
 #pragma unroll
       for (int w = 0; w < kHuffThreads / 32; ++w) {
-        const int c = s_wcount[w];
+        const uint32_t v = s_votes[w];
+        const int c = __popc(v);
         base += w < warp ? c : 0;
         total += c;
+        if (v && front == kHuffThreads) front = w * 32 + __ffs(v) - 1;
       }
       if (total == 0) break;
-      ++rounds, tasks += total;
+      ++rounds, ++local_rounds, tasks += total;
+      if (local_rounds >= kBroadcastEvery && (local_rounds & (local_rounds - 1)) == 0) {
+        // Still repeating after this many rounds (ordinary streams settle in a dozen): the
+        // stream does not resynchronise by itself — flat or periodic content, where every start
+        // phase parses self-consistently — and the exact state would crawl forward one
+        // subsequence per round.  In such a stream the state relative to the subsequence start
+        // repeats (period dividing the subsequence length) or cycles through a few values; the
+        // fronts of the last rounds, one subsequence apart and exact, show that cycle.  Give every
+        // later subsequence the state of the recorded front congruent to it and decode them all
+        // once; if the guess is wrong, the rounds simply go on from there.
+        const uint32_t my_begin = chunk_begin + (uint32_t)tid * kSubseqBits;
+        if (tid == front) {
+          s_hist_p[front & (kHistory - 1)] = np - my_begin, s_hist_bz[front & (kHistory - 1)] = nbz;
+          s_hist_t[front & (kHistory - 1)] = front;
+        }
+        __syncthreads();
+        // smallest q < kHistory / 2 for which the last q fronts repeat the q before them (a cycle
+        // longer than the rounds spent so far cannot be seen yet; the next broadcast will)
+        int cycle = 1;
+        for (int q = 1; q < kHistory / 2; ++q) {
+          bool ok = true;
+          for (int i = front; i > front - q && ok; --i) {
+            const int a = i & (kHistory - 1), b = (i - q) & (kHistory - 1);
+            ok = i - q >= 0 && s_hist_t[a] == i && s_hist_t[b] == i - q && s_hist_p[a] == s_hist_p[b] &&
+                 s_hist_bz[a] == s_hist_bz[b];
+          }
+          if (ok) {
+            cycle = q;
+            break;
+          }
+        }
+        // The guess must not cost a stream that IS converging (slowly: very high qualities need
+        // dozens of rounds) what it has reached: keep the old results in registers, and keep
+        // the guess only if it leaves more subsequences consistent with their predecessors.
+        const uint32_t old_ep = s_entry_p[tid], old_ebz = s_entry_bz[tid];
+        const uint32_t old_xp = s_exit_p[tid], old_xbz = s_exit_bz[tid];
+        const int old_nb = s_nb[tid], old_d0 = s_d0[tid], old_d1 = s_d1[tid], old_d2 = s_d2[tid];
+        const uint8_t old_flag = s_flag[tid];
+        const int agreed_before = __syncthreads_count(tid > front && !redo);
+        if (tid >= front) {
+          const int j = (tid - front) % cycle;  // state of subsequence front - cycle + j (j > 0) or front
+          const int from = (j ? front - cycle + j : front) & (kHistory - 1);
+          // only the front's predecessor is known to be exact
+          s_entry_p[tid] = tid == front ? np : min(my_begin + s_hist_p[from], S.total_bits);
+          s_entry_bz[tid] = tid == front ? nbz : s_hist_bz[from];
+          run(tid);
+        }
+        __syncthreads();
+        const bool agrees = tid > front && s_entry_p[tid] == s_exit_p[tid - 1] && s_entry_bz[tid] == s_exit_bz[tid - 1];
+        const int agreed_after = __syncthreads_count(agrees);
+        // (a tie goes to the guess: a self-consistent but wrong parse of a periodic stream also
+        // "agrees" everywhere, until the front reaches it)
+        if (agreed_after < agreed_before && tid > front) {  // worse: put the old results back
+          s_entry_p[tid] = old_ep, s_entry_bz[tid] = old_ebz;
+          s_exit_p[tid] = old_xp, s_exit_bz[tid] = old_xbz;
+          s_nb[tid] = old_nb, s_d0[tid] = old_d0, s_d1[tid] = old_d1, s_d2[tid] = old_d2;
+          s_flag[tid] = old_flag;
+        }
+        continue;
+      }
+      if (tid == front) {  // remember the front of every round (see the broadcast above)
+        s_hist_p[front & (kHistory - 1)] = np - (chunk_begin + (uint32_t)tid * kSubseqBits);
+        s_hist_bz[front & (kHistory - 1)] = nbz;
+        s_hist_t[front & (kHistory - 1)] = front;
+      }
       if (redo) {
         s_entry_p[tid] = np, s_entry_bz[tid] = nbz;
         s_task[base + __popc(votes & ((1u << lane) - 1u))] = (uint16_t)tid;
