@@ -297,7 +297,8 @@ typedef struct ia_jpeg_job {
   const uint8_t* file_dev; /* the whole file; read in aligned 16-byte units, so the bytes up to the next
                               16-byte boundary after its end must be readable (any cudaMalloc'ed buffer is) */
   uint8_t* clean_dev;      /* entropy-coded bytes without stuffing / RST markers */
-  uint32_t* segment_dev;   /* [0] clean bytes, [1] restart boundaries found, [2..] their clean byte offsets */
+  uint32_t* segment_dev;   /* [0] clean bytes, [1] restart boundaries found, [2..] their clean byte offsets,
+                              [2 + num_segments] 1 = no marker behind the entropy-coded data */
   int16_t* coef_dev;       /* [total_blocks, 64] natural order, DC absolute, not dequantised */
   uint8_t* plane_dev[IA_JPEG_MAX_COMPONENTS]; /* per component, padded to whole MCUs */
   uint8_t* out_dev;        /* uint8 [out_height, out_width, 3] RGB */
@@ -308,8 +309,13 @@ typedef struct ia_jpeg_job {
 
 /* sizeof(ia_jpeg_job) as the library was compiled, for bindings that mirror the struct. */
 size_t ia_jpeg_job_size(void);
-/* Host only.  IA_OK, IA_ERR_INVALID_ARGUMENT (not a JPEG / truncated headers: the reference
- * raises "Failed to decode image from bytes") or IA_ERR_UNSUPPORTED. */
+/* Host only.  IA_OK, IA_ERR_INVALID_ARGUMENT (whatever makes libjpeg give up on the headers,
+ * so that cv2.imdecode returns None and the reference raises "Failed to decode image from
+ * bytes": no FF D8 FF signature, truncated or mis-sized segments, unknown markers, a second
+ * SOI / SOF, sampling factors outside 1..4, missing quantisation tables, Huffman tables whose
+ * codes overflow or whose DC symbols exceed 15, more than 10 blocks per MCU) or
+ * IA_ERR_UNSUPPORTED.  Huffman table ids 0 and 1 default to the standard tables of T.81
+ * Annex K when the file defines none, as libjpeg does for Motion-JPEG frames. */
 int ia_jpeg_parse(const uint8_t* file_host, size_t file_bytes, ia_jpeg_job* job);
 /* Device scratch for n parsed jobs (clean streams, coefficients, planes). */
 size_t ia_jpeg_workspace_bytes(const ia_jpeg_job* jobs_host, int n);
@@ -318,8 +324,12 @@ size_t ia_jpeg_workspace_bytes(const ia_jpeg_job* jobs_host, int n);
 int ia_jpeg_plan(ia_jpeg_job* jobs_host, int n, const uint8_t* const* file_dev,
                  uint8_t* const* out_dev, void* workspace_dev, size_t workspace_bytes);
 /* jobs_dev: the planned job array copied to device memory by the caller (jobs_host is read
- * for launch geometry only).  status_dev int32 [n]: 0 ok, bit 0 = the entropy-coded data
- * ended early or overran (pixels then differ from libjpeg's error concealment). */
+ * for launch geometry only).  status_dev int32 [n]: 0 = the pixels are libjpeg's;
+ * bit 0 = the entropy-coded data held fewer or more blocks than the frame (a damaged stream:
+ * undamaged MCUs are exact, the rest differs from libjpeg's error concealment);
+ * bit 1 = in addition the data simply ends, without a marker behind it, before the last
+ * block — there libjpeg runs out of input, cv2.imdecode returns None and the reference
+ * raises "Failed to decode image from bytes" (shared/processing/jpeg.py raises it too). */
 int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* jobs_dev, int n,
                    int32_t* status_dev, void* stream);
 

@@ -31,6 +31,40 @@ static const uint8_t h_natural[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32
                                       58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
 // =========================================================================== host: headers
+// ITU T.81 Annex K.3-K.6: the tables libjpeg installs for ids 0 (luminance) and 1 (chrominance)
+// when a file defines none.  DC symbols are 0..11 in order for both.
+static const uint8_t kStdDcCounts[2][16] = {{0, 1, 5, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0},
+                                            {0, 3, 1, 1, 1, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0}};
+static const uint8_t kStdAcCounts[2][16] = {{0, 2, 1, 3, 3, 2, 4, 3, 5, 5, 4, 4, 0, 0, 1, 125},
+                                            {0, 2, 1, 2, 4, 4, 3, 4, 7, 5, 4, 4, 0, 1, 2, 119}};
+static const uint8_t kStdAcVals[2][162] = {
+    {
+     0x01, 0x02, 0x03, 0x00, 0x04, 0x11, 0x05, 0x12, 0x21, 0x31, 0x41, 0x06, 0x13, 0x51, 0x61, 0x07,
+     0x22, 0x71, 0x14, 0x32, 0x81, 0x91, 0xA1, 0x08, 0x23, 0x42, 0xB1, 0xC1, 0x15, 0x52, 0xD1, 0xF0,
+     0x24, 0x33, 0x62, 0x72, 0x82, 0x09, 0x0A, 0x16, 0x17, 0x18, 0x19, 0x1A, 0x25, 0x26, 0x27, 0x28,
+     0x29, 0x2A, 0x34, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3A, 0x43, 0x44, 0x45, 0x46, 0x47, 0x48, 0x49,
+     0x4A, 0x53, 0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5A, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68, 0x69,
+     0x6A, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78, 0x79, 0x7A, 0x83, 0x84, 0x85, 0x86, 0x87, 0x88, 0x89,
+     0x8A, 0x92, 0x93, 0x94, 0x95, 0x96, 0x97, 0x98, 0x99, 0x9A, 0xA2, 0xA3, 0xA4, 0xA5, 0xA6, 0xA7,
+     0xA8, 0xA9, 0xAA, 0xB2, 0xB3, 0xB4, 0xB5, 0xB6, 0xB7, 0xB8, 0xB9, 0xBA, 0xC2, 0xC3, 0xC4, 0xC5,
+     0xC6, 0xC7, 0xC8, 0xC9, 0xCA, 0xD2, 0xD3, 0xD4, 0xD5, 0xD6, 0xD7, 0xD8, 0xD9, 0xDA, 0xE1, 0xE2,
+     0xE3, 0xE4, 0xE5, 0xE6, 0xE7, 0xE8, 0xE9, 0xEA, 0xF1, 0xF2, 0xF3, 0xF4, 0xF5, 0xF6, 0xF7, 0xF8,
+     0xF9, 0xFA,
+    },
+    {
+     0x00, 0x01, 0x02, 0x03, 0x11, 0x04, 0x05, 0x21, 0x31, 0x06, 0x12, 0x41, 0x51, 0x07, 0x61, 0x71,
+     0x13, 0x22, 0x32, 0x81, 0x08, 0x14, 0x42, 0x91, 0xA1, 0xB1, 0xC1, 0x09, 0x23, 0x33, 0x52, 0xF0,
+     0x15, 0x62, 0x72, 0xD1, 0x0A, 0x16, 0x24, 0x34, 0xE1, 0x25, 0xF1, 0x17, 0x18, 0x19, 0x1A, 0x26,
+     0x27, 0x28, 0x29, 0x2A, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3A, 0x43, 0x44, 0x45, 0x46, 0x47, 0x48,
+     0x49, 0x4A, 0x53, 0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5A, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68,
+     0x69, 0x6A, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78, 0x79, 0x7A, 0x82, 0x83, 0x84, 0x85, 0x86, 0x87,
+     0x88, 0x89, 0x8A, 0x92, 0x93, 0x94, 0x95, 0x96, 0x97, 0x98, 0x99, 0x9A, 0xA2, 0xA3, 0xA4, 0xA5,
+     0xA6, 0xA7, 0xA8, 0xA9, 0xAA, 0xB2, 0xB3, 0xB4, 0xB5, 0xB6, 0xB7, 0xB8, 0xB9, 0xBA, 0xC2, 0xC3,
+     0xC4, 0xC5, 0xC6, 0xC7, 0xC8, 0xC9, 0xCA, 0xD2, 0xD3, 0xD4, 0xD5, 0xD6, 0xD7, 0xD8, 0xD9, 0xDA,
+     0xE2, 0xE3, 0xE4, 0xE5, 0xE6, 0xE7, 0xE8, 0xE9, 0xEA, 0xF2, 0xF3, 0xF4, 0xF5, 0xF6, 0xF7, 0xF8,
+     0xF9, 0xFA,
+    }};
+
 static inline uint32_t be16(const uint8_t* p) { return ((uint32_t)p[0] << 8) | p[1]; }
 
 // Orientation tag (0x0112) of an APP1 "Exif" payload; 1 when absent or malformed.
@@ -62,36 +96,75 @@ static int exif_orientation(const uint8_t* seg, size_t len) {
   return 1;
 }
 
+// libjpeg's fatal checks on a table a scan uses (jdhuff.c jpeg_make_d_derived_tbl): the codes of
+// a length may not reach the all-ones code of that length; DC symbols are categories 0..15.
+static bool huffman_table_ok(const uint8_t* counts, const uint8_t* vals, bool dc) {
+  int code = 0, total = 0;
+  for (int l = 1; l <= 16; ++l) {
+    code += counts[l - 1];
+    total += counts[l - 1];
+    if (code >= (1 << l)) return false;
+    code <<= 1;
+  }
+  if (dc) {
+    for (int k = 0; k < total; ++k)
+      if (vals[k] > 15) return false;
+  }
+  return true;
+}
+
 static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
   memset(job, 0, sizeof(*job));
-  IA_RETURN_IF(n < 4 || d[0] != 0xFF || d[1] != 0xD8, IA_ERR_INVALID_ARGUMENT);
+  // What makes libjpeg give up (ERREXIT: cv2.imdecode returns None and the reference raises) is
+  // IA_ERR_INVALID_ARGUMENT here; jdmarker.c read_markers / get_sof / get_sos / get_dht / get_dqt /
+  // get_dri, jdinput.c initial_setup / per_scan_setup / latch_quant_tables.  OpenCV picks its
+  // decoder by the three-byte signature FF D8 FF.
+  IA_RETURN_IF(n < 4 || d[0] != 0xFF || d[1] != 0xD8 || d[2] != 0xFF, IA_ERR_INVALID_ARGUMENT);
   IA_RETURN_IF(n >= 0xfffffff0ull, IA_ERR_UNSUPPORTED);
   uint16_t qt[4][64];
   bool have_qt[4] = {false, false, false, false}, have_dc[4] = {false, false, false, false},
-       have_ac[4] = {false, false, false, false};
+       have_ac[4] = {false, false, false, false}, long_dc[4] = {false, false, false, false};
   int tq[IA_JPEG_MAX_COMPONENTS] = {0, 0, 0}, comp_id[IA_JPEG_MAX_COMPONENTS] = {0, 0, 0};
   bool have_sof = false, saw_exif = false, saw_jfif = false;
   int adobe_transform = -1;
   job->orientation = 1;
   size_t i = 2;
   for (;;) {
-    while (i < n && d[i] != 0xFF) ++i;
-    while (i < n && d[i] == 0xFF) ++i;
-    IA_RETURN_IF(i >= n, IA_ERR_INVALID_ARGUMENT);
+    // next_marker: skip to an FF, skip fill FFs; FF00 is stuffing, not a marker
+    for (;;) {
+      while (i < n && d[i] != 0xFF) ++i;
+      while (i < n && d[i] == 0xFF) ++i;
+      IA_RETURN_IF(i >= n, IA_ERR_INVALID_ARGUMENT);
+      if (d[i] != 0) break;
+      ++i;
+    }
     const uint8_t m = d[i++];
-    if (m == 0xD8 || (m >= 0xD0 && m <= 0xD7) || m == 0x01) continue;
-    IA_RETURN_IF(m == 0xD9, IA_ERR_INVALID_ARGUMENT);
+    if ((m >= 0xD0 && m <= 0xD7) || m == 0x01) continue;  // parameterless
+    IA_RETURN_IF(m == 0xD8 || m == 0xD9, IA_ERR_INVALID_ARGUMENT);  // second SOI, EOI before the scan
+    const bool known = (m >= 0xC0 && m <= 0xCF) || m == 0xDA || m == 0xDB || m == 0xDC || m == 0xDD ||
+                       m == 0xFE || (m >= 0xE0 && m <= 0xEF);
+    IA_RETURN_IF(!known, IA_ERR_INVALID_ARGUMENT);
     IA_RETURN_IF(i + 2 > n, IA_ERR_INVALID_ARGUMENT);
-    const size_t L = be16(d + i);
+    size_t L = be16(d + i);
+    // skip_variable / get_interesting_appn skip nothing for a length below 2
+    if (L < 2 && ((m >= 0xE0 && m <= 0xEF) || m == 0xFE || m == 0xDC)) L = 2;
     IA_RETURN_IF(L < 2 || i + L > n, IA_ERR_INVALID_ARGUMENT);
     const uint8_t* seg = d + i + 2;
     const size_t len = L - 2;
+    if (m == 0xCC) {  // DAC: pointless in a Huffman file, but get_dac still checks it
+      IA_RETURN_IF(len % 2, IA_ERR_INVALID_ARGUMENT);
+      for (size_t k = 0; k < len; k += 2) {
+        const int index = seg[k], val = seg[k + 1];
+        IA_RETURN_IF(index >= 32 || (index < 16 && (val & 15) > (val >> 4)), IA_ERR_INVALID_ARGUMENT);
+      }
+    }
     if (m == 0xDB) {
       size_t k = 0;
       while (k < len) {
         const int pq = seg[k] >> 4, t = seg[k] & 15;
         ++k;
-        IA_RETURN_IF(t > 3 || pq > 1 || k + (pq ? 128 : 64) > len, IA_ERR_INVALID_ARGUMENT);
+        // any non-zero precision nibble means 16-bit entries (get_dqt)
+        IA_RETURN_IF(t > 3 || k + (pq ? 128 : 64) > len, IA_ERR_INVALID_ARGUMENT);
         for (int j = 0; j < 64; ++j) {
           qt[t][h_natural[j]] = pq ? (uint16_t)be16(seg + k + 2 * j) : seg[k + j];
         }
@@ -99,24 +172,22 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
         have_qt[t] = true;
       }
     } else if (m == 0xC0 || m == 0xC1) {
-      IA_RETURN_IF(len < 6, IA_ERR_INVALID_ARGUMENT);
-      IA_RETURN_IF(seg[0] != 8, IA_ERR_UNSUPPORTED);
+      IA_RETURN_IF(have_sof || len < 6, IA_ERR_INVALID_ARGUMENT);
       job->height = (int32_t)be16(seg + 1);
       job->width = (int32_t)be16(seg + 3);
       job->ncomp = seg[5];
+      IA_RETURN_IF(job->height == 0 || job->width == 0 || job->ncomp == 0, IA_ERR_INVALID_ARGUMENT);
+      IA_RETURN_IF(len != 6 + 3 * (size_t)job->ncomp, IA_ERR_INVALID_ARGUMENT);
+      IA_RETURN_IF(seg[0] != 8, IA_ERR_UNSUPPORTED);
       IA_RETURN_IF(job->ncomp != 1 && job->ncomp != 3, IA_ERR_UNSUPPORTED);
-      IA_RETURN_IF(len < 6 + 3 * (size_t)job->ncomp, IA_ERR_INVALID_ARGUMENT);
       for (int c = 0; c < job->ncomp; ++c) {
         comp_id[c] = seg[6 + 3 * c];
         job->h[c] = seg[7 + 3 * c] >> 4;
         job->v[c] = seg[7 + 3 * c] & 15;
         tq[c] = seg[8 + 3 * c];
-        IA_RETURN_IF(job->h[c] < 1 || job->h[c] > 4 || job->v[c] < 1 || job->v[c] > 4 || tq[c] > 3,
-                     IA_ERR_INVALID_ARGUMENT);
       }
       have_sof = true;
-    } else if (m == 0xC2 || m == 0xC3 || (m >= 0xC5 && m <= 0xC7) || (m >= 0xC9 && m <= 0xCB) ||
-               (m >= 0xCD && m <= 0xCF)) {
+    } else if (m >= 0xC0 && m <= 0xCF && m != 0xC4 && m != 0xCC) {
       return IA_ERR_UNSUPPORTED;  // progressive, lossless, arithmetic
     } else if (m == 0xC4) {
       size_t k = 0;
@@ -126,43 +197,50 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
         IA_RETURN_IF(tc > 1 || th > 3, IA_ERR_INVALID_ARGUMENT);
         int total = 0;
         for (int j = 0; j < 16; ++j) total += seg[k + 1 + j];
-        IA_RETURN_IF(total > (tc ? 256 : 16) || k + 17 + total > len, IA_ERR_INVALID_ARGUMENT);
+        IA_RETURN_IF(total > 256 || k + 17 + total > len, IA_ERR_INVALID_ARGUMENT);
         uint8_t* counts = tc ? job->ac_counts[th] : job->dc_counts[th];
         uint8_t* vals = tc ? job->ac_vals[th] : job->dc_vals[th];
         memcpy(counts, seg + k + 1, 16);
         memset(vals, 0, tc ? 256 : 16);
-        memcpy(vals, seg + k + 17, total);
+        // a DC table of more than 16 symbols repeats one or holds a category above 15: refused when used
+        if (!tc) long_dc[th] = total > 16;
+        memcpy(vals, seg + k + 17, !tc && total > 16 ? 16 : total);
         (tc ? have_ac : have_dc)[th] = true;
         k += 17 + total;
       }
     } else if (m == 0xDD) {
-      IA_RETURN_IF(len < 2, IA_ERR_INVALID_ARGUMENT);
+      IA_RETURN_IF(len != 2, IA_ERR_INVALID_ARGUMENT);
       job->restart_interval = (int32_t)be16(seg);
     } else if (m == 0xE1 && !saw_exif && len >= 6 && memcmp(seg, "Exif\0\0", 6) == 0) {
       saw_exif = true;
       job->orientation = exif_orientation(seg, len);
     } else if (m == 0xEE && len >= 12 && memcmp(seg, "Adobe", 5) == 0) {
       adobe_transform = seg[11];
-    } else if (m == 0xE0 && len >= 5 && memcmp(seg, "JFIF\0", 5) == 0) {
+    } else if (m == 0xE0 && len >= 14 && memcmp(seg, "JFIF\0", 5) == 0) {
       saw_jfif = true;
     } else if (m == 0xDA) {
-      IA_RETURN_IF(!have_sof || len < 1, IA_ERR_INVALID_ARGUMENT);
-      const int ns = seg[0];
+      IA_RETURN_IF(!have_sof, IA_ERR_INVALID_ARGUMENT);
+      const int ns = len ? seg[0] : 0;
+      IA_RETURN_IF(ns < 1 || ns > 4 || len != 2 * (size_t)ns + 4, IA_ERR_INVALID_ARGUMENT);
+      for (int s = 0; s < ns; ++s) {
+        bool found = false;
+        for (int c = 0; c < job->ncomp; ++c) found |= seg[1 + 2 * s] == comp_id[c];
+        IA_RETURN_IF(!found, IA_ERR_INVALID_ARGUMENT);
+      }
       IA_RETURN_IF(ns != job->ncomp, IA_ERR_UNSUPPORTED);  // non-interleaved / multi-scan
-      IA_RETURN_IF(len < 1 + 2 * (size_t)ns + 3, IA_ERR_INVALID_ARGUMENT);
       for (int s = 0; s < ns; ++s) {
         IA_RETURN_IF(seg[1 + 2 * s] != comp_id[s], IA_ERR_UNSUPPORTED);
         job->comp_dc[s] = seg[2 + 2 * s] >> 4;
         job->comp_ac[s] = seg[2 + 2 * s] & 15;
-        IA_RETURN_IF(job->comp_dc[s] > 3 || job->comp_ac[s] > 3, IA_ERR_INVALID_ARGUMENT);
-        IA_RETURN_IF(!have_dc[job->comp_dc[s]] || !have_ac[job->comp_ac[s]], IA_ERR_INVALID_ARGUMENT);
       }
       job->scan_offset = (uint32_t)(i + L);
       break;
     }
     i += L;
   }
-  IA_RETURN_IF(job->width < 1 || job->height < 1, IA_ERR_INVALID_ARGUMENT);
+  IA_RETURN_IF(job->width > 65500 || job->height > 65500, IA_ERR_INVALID_ARGUMENT);
+  for (int c = 0; c < job->ncomp; ++c)
+    IA_RETURN_IF(job->h[c] < 1 || job->h[c] > 4 || job->v[c] < 1 || job->v[c] > 4, IA_ERR_INVALID_ARGUMENT);
   // libjpeg's guess of the colour space (jdapimin.c default_decompress_parms): JFIF means YCbCr;
   // else an Adobe marker decides; else the component ids 'R','G','B' mean RGB.  RGB is not decoded here.
   if (job->ncomp == 3 && !saw_jfif) {
@@ -172,8 +250,29 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
   if (job->ncomp == 1) job->h[0] = job->v[0] = 1;  // sampling factors mean nothing for one component
   job->hmax = job->vmax = 1;
   int bpm = 0;
+  // Table ids 0 and 1 fall back to the standard tables of T.81 Annex K when the file defines
+  // none (jdhuff.c jinit_huff_decoder -> std_huff_tables: Motion-JPEG frames leave them out).
+  for (int t = 0; t < 2; ++t) {
+    if (!have_dc[t]) {
+      memcpy(job->dc_counts[t], kStdDcCounts[t], 16);
+      memset(job->dc_vals[t], 0, 16);
+      for (int k = 0; k < 12; ++k) job->dc_vals[t][k] = (uint8_t)k;
+      have_dc[t] = true;
+    }
+    if (!have_ac[t]) {
+      memcpy(job->ac_counts[t], kStdAcCounts[t], 16);
+      memset(job->ac_vals[t], 0, 256);
+      memcpy(job->ac_vals[t], kStdAcVals[t], 162);
+      have_ac[t] = true;
+    }
+  }
   for (int c = 0; c < job->ncomp; ++c) {
-    IA_RETURN_IF(!have_qt[tq[c]], IA_ERR_INVALID_ARGUMENT);
+    const int td = job->comp_dc[c], ta = job->comp_ac[c];
+    IA_RETURN_IF(tq[c] > 3 || !have_qt[tq[c]], IA_ERR_INVALID_ARGUMENT);
+    IA_RETURN_IF(td > 3 || ta > 3 || !have_dc[td] || !have_ac[ta] || long_dc[td], IA_ERR_INVALID_ARGUMENT);
+    IA_RETURN_IF(!huffman_table_ok(job->dc_counts[td], job->dc_vals[td], true) ||
+                     !huffman_table_ok(job->ac_counts[ta], job->ac_vals[ta], false),
+                 IA_ERR_INVALID_ARGUMENT);
     memcpy(job->quant[c], qt[tq[c]], sizeof(qt[0]));
     job->hmax = job->h[c] > job->hmax ? job->h[c] : job->hmax;
     job->vmax = job->v[c] > job->vmax ? job->v[c] : job->vmax;
@@ -327,7 +426,7 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
   unstuff_count_kernel<<<dim3(max_tiles, n), kUnstuffThreads, 0, stream>>>(jobs_dev);
   int rc = launch_status();
   if (rc != IA_OK) return rc;
-  unstuff_scan_kernel<<<n, 32, 0, stream>>>(jobs_dev);
+  unstuff_scan_kernel<<<n, 32, 0, stream>>>(jobs_dev, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
   unstuff_scatter_kernel<<<dim3(max_tiles, n), kUnstuffThreads, 0, stream>>>(jobs_dev);

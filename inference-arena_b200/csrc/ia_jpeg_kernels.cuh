@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_count_kernel(const ia
 
 // One warp per image walks the tiles: counts -> exclusive bases; tiles after the end of the
 // scan are marked dead (end = 0).  Also writes the totals and the zero padding.
-__global__ void __launch_bounds__(32) unstuff_scan_kernel(const ia_jpeg_job* __restrict__ jobs) {
+__global__ void __launch_bounds__(32) unstuff_scan_kernel(const ia_jpeg_job* __restrict__ jobs, int32_t* __restrict__ status) {
   const ia_jpeg_job& J = jobs[blockIdx.x];
   const uint32_t tiles = tile_capacity(J);
   const int lane = threadIdx.x;
@@ -183,6 +183,12 @@ __global__ void __launch_bounds__(32) unstuff_scan_kernel(const ia_jpeg_job* __r
   if (lane == 0) {
     J.segment_dev[0] = base_keep;
     J.segment_dev[1] = min(base_bnd, (uint32_t)J.num_segments);
+    // no marker behind the entropy-coded bytes (or a lone FF as the last byte): libjpeg would
+    // run out of input if the blocks are not all there
+    J.segment_dev[2 + J.num_segments] = scan_end == 0xffffffffu || scan_end + 1 >= scan_bytes(J);
+    // the Huffman kernel ORs its findings in; a restart marker count other than the interval
+    // implies is damage already (without an interval libjpeg stops reading at the first one)
+    status[blockIdx.x] = base_bnd + 1 == (uint32_t)J.num_segments ? 0 : 1;
   }
 }
 
@@ -278,7 +284,9 @@ __device__ __forceinline__ uint32_t huff_slow(const HuffTables& T, int slot, uin
   for (int l = kLutBits + 1; l <= 16; ++l) {
     if (code < T.maxcode[slot][l]) return pack_entry(slot, l, T.vals[slot][(T.valoff[slot][l] + (code >> (16 - l))) & 255]);
   }
-  return pack_entry(slot, 16, 0);  // an invalid code eats 16 bits and yields 0 (libjpeg warns and does the same)
+  // an invalid code yields symbol 0 after 17 bits: libjpeg's search loop (jpeg_huff_decode) is only
+  // stopped by the sentinel maxcode[17]
+  return pack_entry(slot, 17, 0);
 }
 
 struct Stream {
@@ -287,6 +295,8 @@ struct Stream {
   const uint32_t* bounds;  // restart boundaries (clean byte offsets), ascending
   int num_bounds;
   int bpm;
+  int seg_blocks;    // blocks per restart segment (0 without restart intervals)
+  int32_t* damaged;  // status word of the image: the write pass ORs 1 into it
 };
 
 __device__ __forceinline__ uint32_t load_be(const uint32_t* __restrict__ words, uint32_t i) {
@@ -313,6 +323,9 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
   if (j > 0 && __ldg(S.bounds + j - 1) * 8u == p) {
     b = 0, z = 0, agg.flag = 1;
     dc0 = dc1 = dc2 = 0;
+    // libjpeg restarts by MCU count, this decoder at the markers: when the two disagree the
+    // stream is damaged (libjpeg conceals the short interval, its pixels differ from here on)
+    if (kWrite && blk != j * S.seg_blocks) atomicOr(S.damaged, 1);
   }
   uint32_t next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
   const uint32_t limit = min(end_bit, S.total_bits);
@@ -345,6 +358,7 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
         break;
       }
       // ran into the padding before a restart marker: new segment
+      if (kWrite && (z != 0 || b != 0 || blk != (j + 1) * S.seg_blocks)) atomicOr(S.damaged, 1);
       p = next_bound, b = 0, z = 0, agg.flag = 1;
       dc0 = dc1 = dc2 = 0;
       ++j;
@@ -371,9 +385,11 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
     dc2 += comp == 2 ? add : 0;
     const int zn = z + (int)(e >> 24);
     if (kWrite) {
-      // every stored symbol lands at zig-zag index zn - 1 (the DC at 0); ZRL / EOB store nothing
-      if ((dc_mode || shift != 32u) && zn <= 64 && blk < total_blocks)
-        blk_ptr[T.natural[(zn - 1) & 63]] = (int16_t)(dc_mode ? (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) : value);
+      // every stored symbol lands at zig-zag index zn - 1 (the DC at 0); ZRL / EOB store nothing.
+      // A run past the end of the block (corrupt data) lands on the last coefficient:
+      // jpeg_natural_order has 16 extra entries, all 63.
+      if ((dc_mode || shift != 32u) && blk < total_blocks)
+        blk_ptr[T.natural[min(zn - 1, 63)]] = (int16_t)(dc_mode ? (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) : value);
     }
     z = zn;
     if (zn >= 64) {  // block complete
@@ -472,6 +488,8 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
   S.bounds = J.segment_dev + 2;
   S.num_bounds = (int)J.segment_dev[1];
   S.bpm = J.blocks_per_mcu;
+  S.seg_blocks = J.restart_interval * J.blocks_per_mcu;
+  S.damaged = status + image;
   const int num_chunks = S.total_bits ? (int)((S.total_bits + kChunkBits - 1) / kChunkBits) : 1;
   if (chunk >= num_chunks) return;  // nothing waits on the spare CTAs of shorter images
   build_tables(J, T);
@@ -699,7 +717,14 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
     my_rec[10] = (uint32_t)rounds | ((uint32_t)min(tasks, 0xffff) << 16);
     __threadfence();
     *reinterpret_cast<volatile uint32_t*>(my_rec + 3) = 1u;
-    if (chunk == num_chunks - 1) status[image] = out.nb == J.total_blocks ? 0 : 1;
+    if (chunk == num_chunks - 1) {
+      // 1: the stream held fewer or more blocks than the frame (damaged: libjpeg conceals, pixels
+      // of the damaged part differ); 2: and it simply ends — no marker behind it — before the
+      // last block: libjpeg runs out of input there and OpenCV reports a failed decode
+      int st = out.nb == J.total_blocks ? 0 : 1;
+      if (out.nb < J.total_blocks && (J.segment_dev[2 + J.num_segments] & 1u)) st |= 2;
+      if (st) atomicOr(status + image, st);
+    }
   }
 
   // ---- write pass from the exact entry state
@@ -719,42 +744,35 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
 // =================================================================================== IDCT
 constexpr int kIdctThreads = 128;
 
-#define IA_FIX_0_298631336 2446
-#define IA_FIX_0_390180644 3196
-#define IA_FIX_0_541196100 4433
-#define IA_FIX_0_765366865 6270
-#define IA_FIX_0_899976223 7373
-#define IA_FIX_1_175875602 9633
-#define IA_FIX_1_501321110 12299
-#define IA_FIX_1_847759065 15137
-#define IA_FIX_1_961570560 16069
-#define IA_FIX_2_053119869 16819
-#define IA_FIX_2_562915447 20995
-#define IA_FIX_3_072711026 25172
+// One 8-point pass of jidctint.c (Loeffler-Ligtenberg-Moschytz, CONST_BITS 13) evaluated the way
+// libjpeg-turbo's SIMD code does (jidctint-sse2 / -avx2), which is what OpenCV runs: the same
+// integers as the C code for every block an encoder can produce, and for out-of-range
+// coefficients (corrupt streams, broken tables) the same wrap-arounds — 16-bit lanes in the
+// sums in0 +- in4, in7 + in3, in5 + in1; rotations as sums of two 16x16 products with the
+// constants pre-combined (pmaddwd); 32-bit sums that wrap; results descaled and packed to
+// 16 bits with saturation.  Inputs hold 16-bit values.
+__device__ __forceinline__ int wrap16(int x) { return (int)(int16_t)(uint16_t)(uint32_t)x; }
 
-// one 8-point pass of jidctint.c; outputs are not yet descaled
+template <int kShift>
 __device__ __forceinline__ void idct8(const int d[8], int o[8]) {
-  int z1 = (d[2] + d[6]) * IA_FIX_0_541196100;
-  const int tmp2 = z1 + d[6] * (-IA_FIX_1_847759065);
-  const int tmp3 = z1 + d[2] * IA_FIX_0_765366865;
-  const int tmp0 = (d[0] + d[4]) << 13, tmp1 = (d[0] - d[4]) << 13;
-  const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
-  int t0 = d[7], t1 = d[5], t2 = d[3], t3 = d[1];
-  z1 = t0 + t3;
-  int z2 = t1 + t2, z3 = t0 + t2, z4 = t1 + t3;
-  const int z5 = (z3 + z4) * IA_FIX_1_175875602;
-  t0 *= IA_FIX_0_298631336, t1 *= IA_FIX_2_053119869, t2 *= IA_FIX_3_072711026, t3 *= IA_FIX_1_501321110;
-  z1 *= -IA_FIX_0_899976223, z2 *= -IA_FIX_2_562915447, z3 *= -IA_FIX_1_961570560, z4 *= -IA_FIX_0_390180644;
-  z3 += z5, z4 += z5;
-  t0 += z1 + z3, t1 += z2 + z4, t2 += z2 + z3, t3 += z1 + z4;
-  o[0] = tmp10 + t3, o[7] = tmp10 - t3, o[1] = tmp11 + t2, o[6] = tmp11 - t2;
-  o[2] = tmp12 + t1, o[5] = tmp12 - t1, o[3] = tmp13 + t0, o[4] = tmp13 - t0;
-}
-
-// libjpeg's range_limit[x & RANGE_MASK] with the table centred on 128
-__device__ __forceinline__ uint32_t range_limit(int x) {
-  const int i = x & 1023;
-  return i < 128 ? i + 128 : (i < 512 ? 255 : (i < 896 ? 0 : i - 896));
+  typedef uint32_t u;
+  const u tmp3 = (u)(d[2] * (4433 + 6270)) + (u)(d[6] * 4433);
+  const u tmp2 = (u)(d[2] * 4433) + (u)(d[6] * (4433 - 15137));
+  const u tmp0 = (u)(wrap16(d[0] + d[4]) * 8192), tmp1 = (u)(wrap16(d[0] - d[4]) * 8192);
+  const u tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+  const int z3 = wrap16(d[7] + d[3]), z4 = wrap16(d[5] + d[1]);
+  const u z3n = (u)(z3 * (9633 - 16069)) + (u)(z4 * 9633);
+  const u z4n = (u)(z3 * 9633) + (u)(z4 * (9633 - 3196));
+  const u t0 = (u)(d[7] * (2446 - 7373)) + (u)(d[1] * -7373) + z3n;
+  const u t3 = (u)(d[7] * -7373) + (u)(d[1] * (12299 - 7373)) + z4n;
+  const u t1 = (u)(d[5] * (16819 - 20995)) + (u)(d[3] * -20995) + z4n;
+  const u t2 = (u)(d[5] * -20995) + (u)(d[3] * (25172 - 20995)) + z3n;
+  auto fin = [](u x) -> int {
+    const int v = (int)(x + (1u << (kShift - 1))) >> kShift;
+    return max(-32768, min(32767, v));
+  };
+  o[0] = fin(tmp10 + t3), o[7] = fin(tmp10 - t3), o[1] = fin(tmp11 + t2), o[6] = fin(tmp11 - t2);
+  o[2] = fin(tmp12 + t1), o[5] = fin(tmp12 - t1), o[3] = fin(tmp13 + t0), o[4] = fin(tmp13 - t0);
 }
 
 __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* __restrict__ jobs) {
@@ -776,36 +794,48 @@ __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* _
   const uint4* __restrict__ src = reinterpret_cast<const uint4*>(J.coef_dev + (size_t)g * 64);
   const uint16_t* q = s_quant[c];
   int ws[64];
+  uint32_t below = 0;  // any coefficient in rows 1..7
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
     const uint4 v = __ldg(src + r);
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    if (r) below |= v.x | v.y | v.z | v.w;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      ws[r * 8 + 2 * i] = (int)(int16_t)(w[i] & 0xffffu) * (int)q[r * 8 + 2 * i];
-      ws[r * 8 + 2 * i + 1] = (int)(int16_t)(w[i] >> 16) * (int)q[r * 8 + 2 * i + 1];
+    for (int i = 0; i < 4; ++i) {  // dequantise in a 16-bit lane (pmullw)
+      ws[r * 8 + 2 * i] = wrap16((int)((w[i] & 0xffffu) * (uint32_t)q[r * 8 + 2 * i]));
+      ws[r * 8 + 2 * i + 1] = wrap16((int)((w[i] >> 16) * (uint32_t)q[r * 8 + 2 * i + 1]));
     }
   }
-  // pass 1: columns, descale by CONST_BITS - PASS1_BITS = 11
+  if (below == 0) {
+    // rows 1..7 empty: every column is its row-0 term << PASS1_BITS, in a 16-bit lane
 #pragma unroll
-  for (int col = 0; col < 8; ++col) {
-    int d[8], o[8];
+    for (int col = 0; col < 8; ++col) {
+      const int v = wrap16(ws[col] << 2);
 #pragma unroll
-    for (int r = 0; r < 8; ++r) d[r] = ws[r * 8 + col];
-    idct8(d, o);
+      for (int r = 0; r < 8; ++r) ws[r * 8 + col] = v;
+    }
+  } else {
+    // pass 1: columns, descale by CONST_BITS - PASS1_BITS = 11
 #pragma unroll
-    for (int r = 0; r < 8; ++r) ws[r * 8 + col] = (o[r] + (1 << 10)) >> 11;
+    for (int col = 0; col < 8; ++col) {
+      int d[8], o[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) d[r] = ws[r * 8 + col];
+      idct8<11>(d, o);
+#pragma unroll
+      for (int r = 0; r < 8; ++r) ws[r * 8 + col] = o[r];
+    }
   }
-  // pass 2: rows, descale by CONST_BITS + PASS1_BITS + 3 = 18, range-limit, store
+  // pass 2: rows, descale by CONST_BITS + PASS1_BITS + 3 = 18, clamp to [-128, 127], + 128, store
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
     int d[8], o[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) d[i] = ws[r * 8 + i];
-    idct8(d, o);
+    idct8<18>(d, o);
     uint32_t px[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) px[i] = range_limit((o[i] + (1 << 17)) >> 18);
+    for (int i = 0; i < 8; ++i) px[i] = (uint32_t)(max(-128, min(127, o[i])) + 128);
     uint2 out;
     out.x = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
     out.y = px[4] | (px[5] << 8) | (px[6] << 16) | (px[7] << 24);

@@ -226,4 +226,9 @@ def decode_jpeg_batch_cuda(blobs: list[bytes], device: torch.device | str | None
 def load_jpeg_from_bytes(image_bytes: bytes) -> np.ndarray:
     """``load_image_from_bytes`` for a baseline JPEG, decoded on the GPU: RGB uint8 [H, W, 3]."""
     batch = decode_jpeg_batch_cuda([image_bytes])
-    return batch.frames[0].cpu().numpy()
+    frame = batch.frames[0].cpu().numpy()  # synchronises
+    if int(batch.status[0]) & 2:
+        # the data ends before the last MCU without a marker behind it: libjpeg runs out of
+        # input, cv2.imdecode returns None and the reference raises (transforms.py:104-105)
+        raise ValueError("Failed to decode image from bytes")
+    return frame

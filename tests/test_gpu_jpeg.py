@@ -189,10 +189,130 @@ def test_corrupt_streams_terminate(M):
 
 
 def test_truncated_stream_is_flagged(M):
+    """Data that ends mid-scan without a marker: libjpeg runs out of input, cv2.imdecode returns
+    None, the reference raises — status bit 1, and load_jpeg_from_bytes raises too.  The same cut
+    closed by an EOI is a damaged but decodable file: bit 0 only, undamaged MCU rows exact."""
     data = W.encode(W.photo(64, 64, seed=2), 90, "420")
-    batch = M.decode_jpeg_batch_cuda([data[: len(data) * 2 // 3]])
+    cut = data[: len(data) * 2 // 3]
+    assert cv2.imdecode(np.frombuffer(cut, np.uint8), cv2.IMREAD_COLOR) is None
+    closed = cut + b"\xff\xd9"
+    want = W.reference_decode(closed)
+    batch = M.decode_jpeg_batch_cuda([cut, closed, data])
     torch.cuda.synchronize()
-    assert batch.status.cpu().tolist() == [1]
+    assert batch.status.cpu().tolist() == [3, 1, 0]
+    got = batch.frames[1].cpu().numpy()
+    assert np.array_equal(got[:16], want[:16])  # the first MCU row was complete
+    with pytest.raises(ValueError, match="Failed to decode"):
+        M.load_jpeg_from_bytes(cut)
+    assert np.array_equal(M.load_jpeg_from_bytes(closed)[:16], want[:16])
+
+
+def _strip_dht(data):
+    out, i = bytearray(data[:2]), 2
+    while True:
+        m, L = data[i + 1], (data[i + 2] << 8) | data[i + 3]
+        if m == 0xDA:
+            return bytes(out + data[i:])
+        if m != 0xC4:
+            out += data[i:i + 2 + L]
+        i += 2 + L
+
+
+def test_motion_jpeg_frames_without_huffman_tables(M):
+    """No DHT segment: the standard tables of T.81 Annex K apply (libjpeg's std_huff_tables)."""
+    blobs, wants = [], []
+    for i, sampling in enumerate(("420", "422", "444")):
+        data = W.encode(W.photo(120 + 8 * i, 200, seed=70 + i), 75, sampling, restart=4 * i)
+        bare = _strip_dht(data)
+        assert len(bare) == len(data) - 4 * 2 - (31 + 181 + 31 + 181)
+        blobs.append(bare)
+        wants.append(W.reference_decode(bare))
+        assert np.array_equal(wants[-1], W.reference_decode(data))
+    gray = _strip_dht(W.encode(W.photo(90, 130, seed=77)[..., 0], 80))
+    blobs.append(gray)
+    wants.append(W.reference_decode(gray))
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0] * len(blobs)
+    for got, want in zip(batch.frames, wants):
+        assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_out_of_range_coefficients_wrap_like_the_simd_idct(M):
+    """Quantisation tables far beyond what the coefficients were coded for: the dequantised values
+    leave 16 bits, and what comes out is defined by libjpeg-turbo's SIMD IDCT (16-bit lanes that
+    wrap, saturating packs), which is what OpenCV runs.  The entropy decode is untouched, so
+    every file must come back with status 0 and cv2's pixels."""
+    rng = np.random.default_rng(5)
+    blobs = []
+    for i, sampling in enumerate(("420", "444", "422", "411")):
+        base = W.encode(W.photo(72, 104, seed=80 + i), 30 + 20 * i, sampling)
+        wide = W.with_16bit_quant_tables(base)
+        for variant in range(4):
+            b = bytearray(wide if variant >= 2 else base)
+            i0 = 2
+            while b[i0 + 1] != 0xDA:
+                L = (b[i0 + 2] << 8) | b[i0 + 3]
+                if b[i0 + 1] == 0xDB:
+                    lo, hi = i0 + 5, i0 + 2 + L  # one table per segment: values follow the Pq/Tq byte
+                    assert hi - lo == (128 if variant >= 2 else 64)
+                    vals = rng.integers(0, 256, hi - lo, dtype=np.uint8)
+                    if variant % 2 == 0:
+                        vals[:] = 0xFF
+                    b[lo:hi] = vals.tobytes()
+                i0 += 2 + L
+            blobs.append(bytes(b))
+    wants = [W.reference_decode(b) for b in blobs]
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0] * len(blobs)
+    for got, want in zip(batch.frames, wants):
+        assert np.array_equal(got.cpu().numpy(), want)
+    assert len(blobs) == 16
+
+
+def test_damaged_headers_decode_like_cv2(M):
+    """scripts/jpeg_header_fuzz.py mutants (random damage to tables and parameters before the
+    scan).  Verdicts: the library refuses exactly the files cv2 refuses (or calls them
+    unsupported); pixels: whenever the device reports status 0 they are cv2's — garbage
+    coefficients from damaged Huffman or quantisation tables included."""
+    import importlib.util
+    import random
+    from pathlib import Path
+
+    spec = importlib.util.spec_from_file_location(
+        "jpeg_header_fuzz", Path(__file__).resolve().parent.parent / "scripts" / "jpeg_header_fuzz.py")
+    fuzz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fuzz)
+    rng = random.Random(23)
+    files = [(f, M.parse_jpeg(f).scan_offset) for f in fuzz.bases()]
+    blobs, wants = [], []
+    for _ in range(1500):
+        base, scan = rng.choice(files)
+        data = fuzz.mutate(rng, base, scan)
+        ref = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)
+        try:
+            M.parse_jpeg(data)
+        except M.UnsupportedJpeg:
+            continue
+        except ValueError:
+            assert ref is None
+            continue
+        assert ref is not None
+        blobs.append(data)
+        wants.append(ref[..., ::-1])
+    assert len(blobs) > 700
+    exact = 0
+    for lo in range(0, len(blobs), 256):
+        batch = M.decode_jpeg_batch_cuda(blobs[lo:lo + 256])
+        torch.cuda.synchronize()
+        status = batch.status.cpu().tolist()
+        for st, got, want in zip(status, batch.frames, wants[lo:lo + 256]):
+            assert tuple(got.shape) == want.shape
+            if st == 0:
+                assert np.array_equal(got.cpu().numpy(), want)
+                exact += 1
+    assert exact > 600
 
 
 def test_two_decoders_on_two_streams(M):
