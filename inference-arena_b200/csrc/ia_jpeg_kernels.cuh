@@ -333,6 +333,7 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
   uint32_t info = T.blk_info[b];                  // component | DC slot << 8 | AC slot << 16
   int16_t* blk_ptr = kWrite ? coef + (size_t)blk * 64 : nullptr;
   int nb = 0;
+  uint32_t tail_from = 0xffffffffu;  // write pass: where the data ran out inside a symbol
 
   // three big-endian words of the stream: (w0:w1) holds bit p, w2 is fetched ahead
   uint32_t w0 = 0, w1 = 0, w2 = 0, widx = 0;
@@ -353,7 +354,10 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
     const uint32_t used = e & 255u, len = (e >> 8) & 255u, shift = (e >> 16) & 255u;
     const uint32_t p_next = p + used;
     if (p_next > stop) {
-      if (p_next > S.total_bits) {  // the padding at the very end: nothing more to decode
+      // (a symbol that starts in the padding before a marker can reach past a short last segment
+      // as well: the boundary comes first)
+      if (next_bound > S.total_bits) {  // the padding at the very end: nothing more to decode
+        if (kWrite) tail_from = p;  // ... unless blocks are missing: see below
         p = S.total_bits;
         break;
       }
@@ -398,6 +402,51 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
       if (kWrite) ++blk, blk_ptr += 64;
       b = b + 1 == S.bpm ? 0 : b + 1;
       info = T.blk_info[b];
+    }
+  }
+  if (kWrite) {
+    // Blocks are missing and the data is over (a file cut short and closed by a marker; intact
+    // restart segments before it): libjpeg supplies zero bits, finishes the MCU in hand from
+    // them — one whole MCU if the data ended exactly between two — and leaves the rest zero
+    // (jdhuff.c decode_mcu, insufficient_data).  The counting passes do not see these blocks,
+    // so the image is still reported as damaged.
+    // one thread owns the end: the one that decoded up to it (the first one if there is no data)
+    const bool owns_end = p_io < S.total_bits || (S.total_bits == 0 && end_bit == (uint32_t)kSubseqBits);
+    if (tail_from == 0xffffffffu && p == S.total_bits && end_bit >= S.total_bits) tail_from = p;
+    if (owns_end && tail_from != 0xffffffffu && stop == S.total_bits && blk < total_blocks) {
+      uint32_t q = tail_from;
+      bool crossed = false;
+      while (blk < total_blocks && !(crossed && b == 0 && z == 0)) {
+        // libjpeg restarts by MCU count: the predictors are reset even when the marker is missing
+        // (and what is left of the last byte, padding, is dropped).  j segments were entered at
+        // their markers; a restart that is due beyond those is one without a marker.
+        if (z == 0 && b == 0 && S.seg_blocks && blk % S.seg_blocks == 0 && blk / S.seg_blocks > j)
+          dc0 = dc1 = dc2 = 0, q = max(q, S.total_bits);
+        uint32_t bits = 0;  // zeros from the end of the data on (the clean stream is zero-padded)
+        if (q < S.total_bits) bits = __funnelshift_l(load_be(S.words, (q >> 5) + 1), load_be(S.words, q >> 5), q);
+        const bool dc_mode = z == 0;
+        const uint32_t slot = dc_mode ? (info >> 8) & 255u : info >> 16;
+        uint32_t e = T.lut[slot][bits >> (32 - kLutBits)];
+        if (e == 0) e = huff_slow(T, (int)slot, bits);
+        const uint32_t len = (e >> 8) & 255u, shift = (e >> 16) & 255u;
+        q += e & 255u;
+        crossed |= q > S.total_bits;
+        const uint32_t tail = bits << len;
+        const int raw = (int)__funnelshift_rc(tail, 0u, shift);
+        const int value = raw + (~((int)tail >> 31) & (1 - (int)(1u << (32u - shift))));
+        const uint32_t comp = info & 255u;
+        if (dc_mode) (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) += value;
+        const int zn = z + (int)(e >> 24);
+        if (dc_mode || shift != 32u)
+          blk_ptr[T.natural[min(zn - 1, 63)]] = (int16_t)(dc_mode ? (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) : value);
+        z = zn;
+        if (zn >= 64) {
+          z = 0, ++blk, blk_ptr += 64;
+          b = b + 1 == S.bpm ? 0 : b + 1;
+          info = T.blk_info[b];
+        }
+      }
+      p = S.total_bits;
     }
   }
   agg.nb += nb;

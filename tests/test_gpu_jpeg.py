@@ -112,6 +112,28 @@ def test_noise_image_long_codes(M):
     assert np.array_equal(M.load_jpeg_from_bytes(data), W.reference_decode(data))
 
 
+def test_one_byte_restart_segments(M):
+    """Flat images with a restart marker after every MCU: segments of one or two bytes, so a
+    symbol that starts in the padding in front of a marker can reach past the whole next
+    segment — also past the last one."""
+    blobs = []
+    for value in (0, 77, 128, 255):
+        flat = np.full((40, 72, 3), value, np.uint8)
+        flat[..., 1] = 255 - value
+        for sampling in W.SAMPLINGS:
+            blobs.append(W.encode(flat, 90, sampling, restart=1))
+            blobs.append(W.encode(flat, 30, sampling, restart=2, optimize=True))
+        blobs.append(W.encode(flat[..., 0], 90, restart=1))
+    ramp = np.zeros((24, 64, 3), np.uint8)
+    ramp[:, 32:] = 200  # a single edge: most segments stay tiny, a few are not
+    blobs += [W.encode(ramp, 95, s, restart=1) for s in W.SAMPLINGS]
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0] * len(blobs)
+    for got, data in zip(batch.frames, blobs):
+        assert np.array_equal(got.cpu().numpy(), W.reference_decode(data))
+
+
 def test_mixed_batch(M):
     """Different sizes, samplings and table sets in one call; two calls in a row."""
     rng = np.random.default_rng(7)
@@ -191,7 +213,8 @@ def test_corrupt_streams_terminate(M):
 def test_truncated_stream_is_flagged(M):
     """Data that ends mid-scan without a marker: libjpeg runs out of input, cv2.imdecode returns
     None, the reference raises — status bit 1, and load_jpeg_from_bytes raises too.  The same cut
-    closed by an EOI is a damaged but decodable file: bit 0 only, undamaged MCU rows exact."""
+    closed by a marker is a damaged but decodable file (bit 0 only): libjpeg finishes the MCU in
+    hand from zero bits and leaves the rest grey, and so does the device."""
     data = W.encode(W.photo(64, 64, seed=2), 90, "420")
     cut = data[: len(data) * 2 // 3]
     assert cv2.imdecode(np.frombuffer(cut, np.uint8), cv2.IMREAD_COLOR) is None
@@ -200,11 +223,44 @@ def test_truncated_stream_is_flagged(M):
     batch = M.decode_jpeg_batch_cuda([cut, closed, data])
     torch.cuda.synchronize()
     assert batch.status.cpu().tolist() == [3, 1, 0]
-    got = batch.frames[1].cpu().numpy()
-    assert np.array_equal(got[:16], want[:16])  # the first MCU row was complete
+    assert np.array_equal(batch.frames[1].cpu().numpy(), want)
+    assert (want[-8:] == 128).all()
     with pytest.raises(ValueError, match="Failed to decode"):
         M.load_jpeg_from_bytes(cut)
-    assert np.array_equal(M.load_jpeg_from_bytes(closed)[:16], want[:16])
+    assert np.array_equal(M.load_jpeg_from_bytes(closed), want)
+
+
+@pytest.mark.parametrize("sampling,kw", [("420", {}), ("444", {"optimize": True}), ("422", {"restart": 3}),
+                                         ("gray", {}), ("411", {"restart": 1})])
+def test_scans_cut_short_are_concealed_like_libjpeg(M, sampling, kw):
+    """Every way a scan can stop early at a marker — inside a code, inside the magnitude bits, at
+    a block or MCU boundary, after whole restart segments — against cv2: pixels equal, status 1."""
+    img = W.photo(56, 88, seed=31)
+    data = W.encode(img[..., 0], 85) if sampling == "gray" else W.encode(img, 85, sampling, **kw)
+    scan = J.parse(data)["scan_start"]
+    body = len(data) - 2 - scan
+    blobs, wants = [data[:scan] + b"\xff\xd9"], []  # no entropy-coded data at all
+    for k in range(40):
+        cut = scan + 1 + (k * 37) % (body - 1) if k < 30 else scan + body - (k - 29)
+        tail = (b"\xff\xd9", b"\xff\xc4\x00\x02", b"\xff\xfe")[k % 3]
+        blobs.append(data[:cut] + tail)
+    for blob in blobs:
+        ref = cv2.imdecode(np.frombuffer(blob, np.uint8), cv2.IMREAD_COLOR)
+        wants.append(None if ref is None else ref[..., ::-1])
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    status = batch.status.cpu().tolist()
+    compared = 0
+    for blob, st, got, want in zip(blobs, status, batch.frames, wants):
+        if want is None:
+            continue  # a restart came due and libjpeg's search for its marker ran off the end
+        assert st in (0, 1)
+        if st == 0:  # the cut fell into the padding of the last byte
+            assert np.array_equal(got.cpu().numpy(), want)
+            continue
+        assert np.array_equal(got.cpu().numpy(), want), (sampling, len(blob))
+        compared += 1
+    assert compared >= 25
 
 
 def _strip_dht(data):
