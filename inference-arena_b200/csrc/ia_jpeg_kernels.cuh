@@ -49,8 +49,12 @@ __host__ __device__ inline uint32_t chunk_capacity(const ia_jpeg_job& j) {
 // is the scan-relative position of the thread's first byte and may be negative for the very
 // first thread; bytes outside [0, n) are never kept (before the scan they read as 0, after it
 // as an EOI marker).
-__device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n, uint32_t v0, uint8_t (&b)[18],
-                                         uint32_t& keep_mask, uint32_t& bnd_mask, uint32_t& my_end, long long& r_first) {
+//
+// rst_restarts: the frame has a restart interval.  Without one libjpeg never consumes an RSTn
+// marker: like any other marker it ends the data.
+__device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n, uint32_t v0, bool rst_restarts,
+                                         uint8_t (&b)[18], uint32_t& keep_mask, uint32_t& bnd_mask, uint32_t& my_end,
+                                         long long& r_first) {
   const uint32_t a = (uint32_t)((uintptr_t)src & 15);
   const uint8_t* __restrict__ base = src - a;
   const uint32_t nv = n + a;  // length of the aligned stream that still belongs to the scan
@@ -78,9 +82,9 @@ __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32
     if (r < n) {
       if (cur == 0xFF) {
         if (next == 0x00) keep_mask |= 1u << k;
-        else if (next != 0xFF && !(next >= 0xD0 && next <= 0xD7)) my_end = min(my_end, r);
+        else if (next != 0xFF && !(rst_restarts && next >= 0xD0 && next <= 0xD7)) my_end = min(my_end, r);
       } else if (prev == 0xFF) {
-        if (cur >= 0xD0 && cur <= 0xD7) bnd_mask |= 1u << k;  // cur == 0 is stuffing: dropped
+        if (rst_restarts && cur >= 0xD0 && cur <= 0xD7) bnd_mask |= 1u << k;  // cur == 0 is stuffing: dropped
       } else {
         keep_mask |= 1u << k;
       }
@@ -134,7 +138,7 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_count_kernel(const ia
   uint8_t b[18];
   uint32_t keep_mask, bnd_mask, my_end;
   long long r_first;
-  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end, r_first);
+  classify(J.file_dev + J.scan_offset, n, r0, J.restart_interval != 0, b, keep_mask, bnd_mask, my_end, r_first);
   if (my_end != 0xffffffffu) atomicMin(&s_end, my_end);
   __syncthreads();
   const uint32_t end = s_end;
@@ -205,7 +209,7 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
   uint8_t b[18];
   uint32_t keep_mask, bnd_mask, my_end;
   long long r_first;
-  classify(J.file_dev + J.scan_offset, n, r0, b, keep_mask, bnd_mask, my_end, r_first);
+  classify(J.file_dev + J.scan_offset, n, r0, J.restart_interval != 0, b, keep_mask, bnd_mask, my_end, r_first);
   cut_at(end, r_first, keep_mask, bnd_mask);
   uint32_t total;
   const uint32_t excl = cta_scan_packed((uint32_t)__popc(keep_mask) | ((uint32_t)__popc(bnd_mask) << 16), s_warp, total);

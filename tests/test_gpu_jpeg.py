@@ -263,6 +263,47 @@ def test_scans_cut_short_are_concealed_like_libjpeg(M, sampling, kw):
     assert compared >= 25
 
 
+def test_bit_errors_without_restart_markers_decode_like_libjpeg(M):
+    """Flipped bytes, stray FFs and stray markers (RSTn too: without a restart interval libjpeg
+    never consumes one, it ends the data) in the entropy-coded bytes of files without restart
+    markers.  The garbage that follows — runs past the end of a block, invalid codes, predictors
+    that leave 16 bits, too few or too many blocks — comes out as libjpeg's, pixel for pixel."""
+    rng = np.random.default_rng(3)
+    blobs = []
+    for i, sampling in enumerate(("420", "444", "422", "gray", "411")):
+        img = W.photo(72, 120, seed=50 + i)
+        good = W.encode(img[..., 0], 80) if sampling == "gray" else W.encode(img, 80, sampling, optimize=bool(i & 1))
+        start = J.parse(good)["scan_start"]
+        for k in range(20):
+            b = bytearray(good)
+            for _ in range(1 + k % 3):
+                pos = int(rng.integers(start, len(b) - 3))
+                if k % 4 == 0:
+                    b[pos] = int(rng.integers(0, 256))
+                elif k % 4 == 1:
+                    b[pos] ^= 1 << int(rng.integers(0, 8))
+                elif k % 4 == 2:
+                    b[pos] = 0xFF
+                else:
+                    b[pos:pos + 2] = bytes([0xFF, int(rng.integers(0xD0, 0xD8))])
+            blobs.append(bytes(b))
+    wants = []
+    for blob in blobs:
+        ref = cv2.imdecode(np.frombuffer(blob, np.uint8), cv2.IMREAD_COLOR)
+        wants.append(None if ref is None else ref[..., ::-1])
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    status = batch.status.cpu().tolist()
+    compared = damaged = 0
+    for st, got, want in zip(status, batch.frames, wants):
+        if want is None:
+            continue
+        assert np.array_equal(got.cpu().numpy(), want)
+        compared += 1
+        damaged += st != 0
+    assert compared >= 90 and damaged >= 30
+
+
 def _strip_dht(data):
     out, i = bytearray(data[:2]), 2
     while True:
