@@ -266,7 +266,7 @@ struct Agg {  // what a run of the stream contributes: completed blocks, DC sums
 
 __device__ __forceinline__ Agg combine(const Agg& a, const Agg& b) {
   Agg r;
-  r.nb = a.nb + b.nb;
+  r.nb = b.flag ? b.nb : a.nb + b.nb;  // blocks since the last restart boundary
   if (b.flag) r.flag = 1, r.d0 = b.d0, r.d1 = b.d1, r.d2 = b.d2;
   else r.flag = a.flag, r.d0 = a.d0 + b.d0, r.d1 = a.d1 + b.d1, r.d2 = a.d2 + b.d2;
   return r;
@@ -307,11 +307,62 @@ __device__ __forceinline__ uint32_t load_be(const uint32_t* __restrict__ words, 
   return __byte_perm(__ldg(words + i), 0, 0x0123);
 }
 
-// Decode from state (p, b, z) while p < end_bit.  kWrite: store coefficients of block `blk`
-// onwards with the DC predictors in agg.d*; otherwise only count (agg.d* accumulate the diffs).
+// What libjpeg does when a restart segment (or the whole scan) stops short of its blocks at a
+// marker (jdhuff.c decode_mcu, insufficient_data): it supplies zero bits, finishes the MCU in
+// hand from them — a whole one if the data ended exactly between two — and leaves the rest
+// zero.  q: bit position to go on from; end_pos: where the real bits stop; limit_blk: first
+// block that is not this segment's.  Cold path of the write pass.
+struct TailState {
+  int b, z, blk, dc0, dc1, dc2;
+};
+
+__device__ __noinline__ void conceal(const Stream& S, const HuffTables& T, TailState& s, uint32_t q, uint32_t end_pos,
+                                     int limit_blk, int j, int16_t* __restrict__ coef) {
+  bool crossed = false;
+  uint32_t info = T.blk_info[s.b];
+  while (s.blk < limit_blk && !(crossed && s.b == 0 && s.z == 0)) {
+    // libjpeg restarts by MCU count: the predictors are reset even when the marker is missing
+    // (and what is left of the last byte, padding, is dropped).  j segments were entered at
+    // their markers; a restart that is due beyond those is one without a marker.
+    if (s.z == 0 && s.b == 0 && S.seg_blocks && s.blk % S.seg_blocks == 0 && s.blk / S.seg_blocks > j)
+      s.dc0 = s.dc1 = s.dc2 = 0, q = max(q, end_pos);
+    uint32_t bits = 0;
+    if (q < end_pos) {
+      bits = __funnelshift_l(__byte_perm(__ldg(S.words + (q >> 5) + 1), 0, 0x0123),
+                             __byte_perm(__ldg(S.words + (q >> 5)), 0, 0x0123), q);
+      if (end_pos - q < 32u) bits &= ~(0xffffffffu >> (end_pos - q));
+    }
+    const bool dc_mode = s.z == 0;
+    const uint32_t slot = dc_mode ? (info >> 8) & 255u : info >> 16;
+    uint32_t e = T.lut[slot][bits >> (32 - kLutBits)];
+    if (e == 0) e = huff_slow(T, (int)slot, bits);
+    const uint32_t len = (e >> 8) & 255u, shift = (e >> 16) & 255u;
+    q += e & 255u;
+    crossed |= q > end_pos;
+    const uint32_t tail = bits << len;
+    const int raw = (int)__funnelshift_rc(tail, 0u, shift);
+    const int value = raw + (~((int)tail >> 31) & (1 - (int)(1u << (32u - shift))));
+    const uint32_t comp = info & 255u;
+    int& dc = comp == 0 ? s.dc0 : (comp == 1 ? s.dc1 : s.dc2);
+    if (dc_mode) dc += value;
+    const int zn = s.z + (int)(e >> 24);
+    if (dc_mode || shift != 32u) coef[(size_t)s.blk * 64 + T.natural[min(zn - 1, 63)]] = (int16_t)(dc_mode ? dc : value);
+    s.z = zn;
+    if (zn >= 64) {
+      s.z = 0, ++s.blk;
+      s.b = s.b + 1 == S.bpm ? 0 : s.b + 1;
+      info = T.blk_info[s.b];
+    }
+  }
+}
+
+// Decode from state (p, b, z) while p < end_bit.  kWrite: store coefficients with the DC
+// predictors in agg.d*, `since` = blocks completed since the last restart boundary before p
+// (a segment's blocks start at segment index x blocks per interval, as libjpeg restarts by MCU
+// count); otherwise only count (agg.nb = blocks since the last boundary, agg.d* the diffs).
 template <bool kWrite>
 __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& T, uint32_t& p_io, int& b_io,
-                                             int& z_io, uint32_t end_bit, Agg& agg, int blk,
+                                             int& z_io, uint32_t end_bit, Agg& agg, int since,
                                              int16_t* __restrict__ coef, int total_blocks) {
   uint32_t p = p_io;
   int b = b_io, z = z_io;
@@ -325,16 +376,26 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
   int j = lo;
   int dc0 = agg.d0, dc1 = agg.d1, dc2 = agg.d2;
   if (j > 0 && __ldg(S.bounds + j - 1) * 8u == p) {
+    if (kWrite && S.seg_blocks && (z != 0 || b != 0 || (since != 0 && since != S.seg_blocks))) {
+      // the predecessor stopped exactly here without stepping over the boundary (it would have
+      // handed over a count of 0), and the segment that ends here is damaged
+      atomicOr(S.damaged, 1);
+      if (since < S.seg_blocks) {
+        TailState ts = {b, z, (j - 1) * S.seg_blocks + since, dc0, dc1, dc2};
+        conceal(S, T, ts, p, p, min(total_blocks, j * S.seg_blocks), j - 1, coef);
+      }
+    }
     b = 0, z = 0, agg.flag = 1;
     dc0 = dc1 = dc2 = 0;
-    // libjpeg restarts by MCU count, this decoder at the markers: when the two disagree the
-    // stream is damaged (libjpeg conceals the short interval, its pixels differ from here on)
-    if (kWrite && blk != j * S.seg_blocks) atomicOr(S.damaged, 1);
+    since = 0;
   }
   uint32_t next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
   const uint32_t limit = min(end_bit, S.total_bits);
   uint32_t stop = min(S.total_bits, next_bound);  // no symbol may cross this bit
   uint32_t info = T.blk_info[b];                  // component | DC slot << 8 | AC slot << 16
+  // segment j owns blocks [j * seg_blocks, seg_end); what a damaged segment decodes beyond is dropped
+  int blk = j * S.seg_blocks + since;
+  int seg_end = S.seg_blocks ? min(total_blocks, (j + 1) * S.seg_blocks) : total_blocks;
   int16_t* blk_ptr = kWrite ? coef + (size_t)blk * 64 : nullptr;
   int nb = 0;
   uint32_t tail_from = 0xffffffffu;  // write pass: where the data ran out inside a symbol
@@ -366,7 +427,19 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
         break;
       }
       // ran into the padding before a restart marker: new segment
-      if (kWrite && (z != 0 || b != 0 || blk != (j + 1) * S.seg_blocks)) atomicOr(S.damaged, 1);
+      if (kWrite) {
+        const int next_first = (j + 1) * S.seg_blocks;
+        if (z != 0 || b != 0 || blk != next_first) {  // too few or too many blocks: a damaged segment
+          atomicOr(S.damaged, 1);
+          if (blk < seg_end) {
+            TailState ts = {b, z, blk, dc0, dc1, dc2};
+            conceal(S, T, ts, p, next_bound, seg_end, j, coef);
+          }
+        }
+        blk = next_first, blk_ptr = coef + (size_t)blk * 64;
+        seg_end = min(total_blocks, next_first + S.seg_blocks);
+      }
+      nb = 0;  // blocks are counted from the last boundary
       p = next_bound, b = 0, z = 0, agg.flag = 1;
       dc0 = dc1 = dc2 = 0;
       ++j;
@@ -396,7 +469,7 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
       // every stored symbol lands at zig-zag index zn - 1 (the DC at 0); ZRL / EOB store nothing.
       // A run past the end of the block (corrupt data) lands on the last coefficient:
       // jpeg_natural_order has 16 extra entries, all 63.
-      if ((dc_mode || shift != 32u) && blk < total_blocks)
+      if ((dc_mode || shift != 32u) && blk < seg_end)
         blk_ptr[T.natural[min(zn - 1, 63)]] = (int16_t)(dc_mode ? (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) : value);
     }
     z = zn;
@@ -418,38 +491,12 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
     const bool owns_end = p_io < S.total_bits || (S.total_bits == 0 && end_bit == (uint32_t)kSubseqBits);
     if (tail_from == 0xffffffffu && p == S.total_bits && end_bit >= S.total_bits) tail_from = p;
     if (owns_end && tail_from != 0xffffffffu && stop == S.total_bits && blk < total_blocks) {
+      // (beyond this segment's blocks too when the data ended at or after its last MCU and the
+      // restart that is due has no marker: one more MCU from zeros, predictors reset)
+      TailState ts = {b, z, blk, dc0, dc1, dc2};
       uint32_t q = tail_from;
-      bool crossed = false;
-      while (blk < total_blocks && !(crossed && b == 0 && z == 0)) {
-        // libjpeg restarts by MCU count: the predictors are reset even when the marker is missing
-        // (and what is left of the last byte, padding, is dropped).  j segments were entered at
-        // their markers; a restart that is due beyond those is one without a marker.
-        if (z == 0 && b == 0 && S.seg_blocks && blk % S.seg_blocks == 0 && blk / S.seg_blocks > j)
-          dc0 = dc1 = dc2 = 0, q = max(q, S.total_bits);
-        uint32_t bits = 0;  // zeros from the end of the data on (the clean stream is zero-padded)
-        if (q < S.total_bits) bits = __funnelshift_l(load_be(S.words, (q >> 5) + 1), load_be(S.words, q >> 5), q);
-        const bool dc_mode = z == 0;
-        const uint32_t slot = dc_mode ? (info >> 8) & 255u : info >> 16;
-        uint32_t e = T.lut[slot][bits >> (32 - kLutBits)];
-        if (e == 0) e = huff_slow(T, (int)slot, bits);
-        const uint32_t len = (e >> 8) & 255u, shift = (e >> 16) & 255u;
-        q += e & 255u;
-        crossed |= q > S.total_bits;
-        const uint32_t tail = bits << len;
-        const int raw = (int)__funnelshift_rc(tail, 0u, shift);
-        const int value = raw + (~((int)tail >> 31) & (1 - (int)(1u << (32u - shift))));
-        const uint32_t comp = info & 255u;
-        if (dc_mode) (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) += value;
-        const int zn = z + (int)(e >> 24);
-        if (dc_mode || shift != 32u)
-          blk_ptr[T.natural[min(zn - 1, 63)]] = (int16_t)(dc_mode ? (comp == 0 ? dc0 : (comp == 1 ? dc1 : dc2)) : value);
-        z = zn;
-        if (zn >= 64) {
-          z = 0, ++blk, blk_ptr += 64;
-          b = b + 1 == S.bpm ? 0 : b + 1;
-          info = T.blk_info[b];
-        }
-      }
+      if (blk >= seg_end) ts = {0, 0, seg_end, 0, 0, 0}, q = S.total_bits;  // what a damaged segment had beyond its blocks is skipped
+      if (ts.blk < total_blocks) conceal(S, T, ts, q, S.total_bits, total_blocks, j, coef);
       p = S.total_bits;
     }
   }
@@ -774,8 +821,11 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
       // 1: the stream held fewer or more blocks than the frame (damaged: libjpeg conceals, pixels
       // of the damaged part differ); 2: and it simply ends — no marker behind it — before the
       // last block: libjpeg runs out of input there and OpenCV reports a failed decode
-      int st = out.nb == J.total_blocks ? 0 : 1;
-      if (out.nb < J.total_blocks && (J.segment_dev[2 + J.num_segments] & 1u)) st |= 2;
+      // (out.nb counts from the last restart boundary; the segments before it are checked where
+      // the write pass steps over their boundaries)
+      const int want_nb = J.total_blocks - S.num_bounds * S.seg_blocks;
+      int st = out.nb == want_nb ? 0 : 1;
+      if (out.nb < want_nb && (J.segment_dev[2 + J.num_segments] & 1u)) st |= 2;
       if (st) atomicOr(status + image, st);
     }
   }

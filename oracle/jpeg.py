@@ -430,7 +430,8 @@ def decode_coefficients(data: bytes, info: dict, report: dict | None = None):
     for m in range(mcux * mcuy):
         if ri:
             if to_go == 0:
-                clean = br.marker == 0xD0 + next_rst or (br.marker == 0 and not br.insufficient)
+                # an intact segment leaves the expected marker pending behind less than a byte of padding
+                clean = br.marker == 0xD0 + next_rst and not br.insufficient and br.n < 8
                 br.restart(next_rst)
                 damaged |= not clean or br.marker != 0
                 next_rst = (next_rst + 1) & 7

@@ -304,6 +304,45 @@ def test_bit_errors_without_restart_markers_decode_like_libjpeg(M):
     assert compared >= 90 and damaged >= 30
 
 
+def _bit_errors_inside_restart_segments(seed=9, per_file=16):
+    """Files with restart intervals whose entropy-coded bytes carry bit errors while every
+    marker stays where it was: some segments come out short, some long."""
+    rng = np.random.default_rng(seed)
+    blobs = []
+    for i, (sampling, ri) in enumerate((("420", 1), ("444", 3), ("422", 5), ("gray", 2), ("411", 4), ("420", 11))):
+        img = W.photo(88, 136, seed=60 + i)
+        good = W.encode(img[..., 0], 85, restart=ri) if sampling == "gray" else \
+            W.encode(img, 85, sampling, restart=ri, optimize=bool(i & 1))
+        start = J.parse(good)["scan_start"]
+        for k in range(per_file):
+            b = bytearray(good)
+            hits = 0
+            while hits < 1 + k % 4:
+                pos = int(rng.integers(start + 1, len(b) - 3))
+                new = int(rng.integers(0, 255)) if k % 2 else b[pos] ^ (1 << int(rng.integers(0, 8)))
+                if 0xFF in (b[pos - 1], b[pos], b[pos + 1], new):
+                    continue  # leave markers and stuffing alone
+                b[pos] = new
+                hits += 1
+            blobs.append(bytes(b))
+    return blobs
+
+
+def test_bit_errors_inside_restart_segments_decode_like_libjpeg(M):
+    """libjpeg restarts by MCU count: a segment that runs out of data early is finished from
+    zero bits and padded with zero MCUs, one that has data left over loses it, and the next
+    segment starts at its own MCU either way.  Same pixels as cv2, status 1."""
+    blobs = _bit_errors_inside_restart_segments()
+    wants = [W.reference_decode(b) for b in blobs]
+    batch = M.decode_jpeg_batch_cuda(blobs)
+    torch.cuda.synchronize()
+    status = batch.status.cpu().tolist()
+    # (Huffman codes resynchronise: most bit errors leave the block count of their segment intact)
+    assert set(status) <= {0, 1} and sum(status) >= 5, status
+    for n, (got, want) in enumerate(zip(batch.frames, wants)):
+        assert np.array_equal(got.cpu().numpy(), want), n
+
+
 def _strip_dht(data):
     out, i = bytearray(data[:2]), 2
     while True:
