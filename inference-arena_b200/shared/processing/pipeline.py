@@ -31,6 +31,10 @@ class PipelineOutput:
     crops: torch.Tensor        # float32 [roi_capacity,3,224,224]
     roi_offsets: torch.Tensor  # int32   [N+1]
     rois: torch.Tensor         # int32   [roi_capacity,8]
+    # JPEG input only, int32 [N]: 0 = libjpeg's pixels; bit 0 = damaged stream (concealed the way
+    # libjpeg does, see ia_jpeg_decode); bit 1 = the data ends before the last block without a
+    # marker — the reference raises "Failed to decode image from bytes" for that request
+    jpeg_status: torch.Tensor | None = None
 
 
 class DevicePipeline:
@@ -147,7 +151,10 @@ class RaggedPipeline:
             if self._decoder is None:
                 from .jpeg import JpegDecoder
                 self._decoder = JpegDecoder(self.device)
-            frames = self._decoder.decode([bytes(f) for f in frames]).frames
+            decoded = self._decoder.decode([bytes(f) for f in frames])
+            frames, jpeg_status = decoded.frames, decoded.status
+        else:
+            jpeg_status = None
         n = len(frames)
         need = D.lib().ia_decode_nms_workspace_bytes(n, self.anchors, self.max_candidates)
         if self._workspace is None or self._workspace.numel() < need:
@@ -158,7 +165,7 @@ class RaggedPipeline:
             workspace=self._workspace)
         crops, offsets, rois = D.crop_ragged_cuda(frames, dets, count, self.target, self.crop_size,
                                                   roi_capacity=n * self.rois_per_image)
-        return PipelineOutput(tensor, dets, keep, count, status, crops, offsets, rois)
+        return PipelineOutput(tensor, dets, keep, count, status, crops, offsets, rois, jpeg_status)
 
 
 class HostTicket:
@@ -218,6 +225,7 @@ class HostPipeline:
             "keep": pinned((max_batch, p.max_det), torch.int32),
             "count": pinned((max_batch,), torch.int32),
             "status": pinned((max_batch,), torch.int32),
+            "jpeg_status": pinned((max_batch,), torch.int32),
             "crops": pinned((max_batch * self.rpi, 3, p.crop_size, p.crop_size), torch.float32),
             "roi_offsets": pinned((nchunks, chunk + 1), torch.int32),
         } for _ in range(self.RESULT_SETS)]
@@ -281,7 +289,7 @@ class HostPipeline:
         res = self.results[rs]
         p = self.pipes[0]
         per_image = (3 * p.target * p.target * 4 if tensors_to_host else 0) + p.max_det * (6 * 4 + 4) + 4 + 4
-        self.last_d2h_bytes = n * per_image
+        self.last_d2h_bytes = n * (per_image + (4 if jpeg else 0))  # + the decode status of each file
         cur = torch.cuda.current_stream(self.device)
         for s in self.streams:
             s.wait_stream(cur)
@@ -316,7 +324,8 @@ class HostPipeline:
                     dh.copy_(heads[lo:hi], non_blocking=True)  # first: the copy engine never waits for a kernel
                     self.last_h2d_bytes += dh.numel() * 4
                 if jpeg:
-                    self._decoders[slot].launch(ready, out=[df[i] for i in range(m)])
+                    decoded = self._decoders[slot].launch(ready, out=[df[i] for i in range(m)])
+                    res["jpeg_status"][lo:hi].copy_(decoded.status, non_blocking=True)
                     self.last_h2d_bytes += sum(len(b) for b in frames[lo:hi])
                 else:
                     df.copy_(frames[lo:hi], non_blocking=True)
@@ -337,6 +346,7 @@ class HostPipeline:
             pending = (slot, ev, res, ci, lo, m, out.crops) if tensors_to_host else None
         views = {"tensor": res["tensor"][:n], "dets": res["dets"][:n], "keep": res["keep"][:n],
                  "count": res["count"][:n], "status": res["status"][:n], "crops": res["crops"],
+                 "jpeg_status": res["jpeg_status"][:n] if jpeg else None,
                  "roi_offsets": res["roi_offsets"]}
         ticket = HostTicket(self, sorted(used), pending, views)
         self._tickets[rs] = ticket

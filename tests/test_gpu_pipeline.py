@@ -161,3 +161,32 @@ def test_ragged_pipeline_from_mixed_jpeg_files():
             assert np.array_equal(out.tensor[i : i + 1].cpu().numpy(), tensor), shapes[i]
             assert np.array_equal(out.dets[i, :k].cpu().numpy(), dets)
             assert np.array_equal(out.crops[offs[i] : offs[i + 1]].cpu().numpy(), crops), shapes[i]
+
+
+def test_pipelines_report_the_decode_status_of_each_file():
+    """A damaged upload must not go unnoticed inside a batch: both pipelines hand back the JPEG
+    decode status per request (0 ok, bit 0 damaged and concealed like libjpeg, bit 1 the data
+    simply ends — the request the reference answers with "Failed to decode image from bytes")."""
+    pytest.importorskip("cv2")
+    from shared.processing.pipeline import HostPipeline, RaggedPipeline
+    from workloads import jpeg_cases as W
+
+    h, w = 240, 320
+    files = [W.encode(W.photo(h, w, seed=40 + i), 85, "420") for i in range(6)]
+    files[1] = files[1][: len(files[1]) // 2]                # cut off: no marker behind the data
+    files[4] = files[4][: len(files[4]) // 2] + b"\xff\xd9"  # cut off and closed
+    want = [0, 3, 0, 0, 1, 0]
+    heads = torch.from_numpy(synth.head_v5(len(files), seed=41))
+    out = RaggedPipeline("cuda").run(files, heads.cuda())
+    torch.cuda.synchronize()
+    assert out.jpeg_status.cpu().tolist() == want
+    assert RaggedPipeline("cuda").run([torch.zeros(8, 8, 3, dtype=torch.uint8, device="cuda")],
+                                      heads[:1].cuda()).jpeg_status is None
+    host = HostPipeline(8, h, w, chunk=4)
+    res = host.run(files, heads.pin_memory())
+    assert res["jpeg_status"].tolist() == want
+    frame = W.reference_decode(files[4])  # the concealed frame is libjpeg's, so is everything after it
+    tensor, dets, keep, _, crops = O.run_image(frame, heads[4].numpy(), 0.25, 0.45)
+    assert np.array_equal(res["tensor"][4:5].numpy(), tensor)
+    raw = host.run(torch.zeros(2, h, w, 3, dtype=torch.uint8).pin_memory(), heads[:2].pin_memory())
+    assert raw["jpeg_status"] is None
