@@ -429,7 +429,7 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
   unstuff_scan_kernel<<<n, 32, 0, stream>>>(jobs_dev, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
-  unstuff_scatter_kernel<<<dim3(max_tiles, n), kUnstuffThreads, 0, stream>>>(jobs_dev);
+  unstuff_scatter_kernel<<<dim3(max_tiles, n), kUnstuffThreads, 0, stream>>>(jobs_dev, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
   huffman_kernel<<<max_chunks * (unsigned)n, kHuffThreads, 0, stream>>>(

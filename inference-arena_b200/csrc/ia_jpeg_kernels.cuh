@@ -196,7 +196,8 @@ __global__ void __launch_bounds__(32) unstuff_scan_kernel(const ia_jpeg_job* __r
   }
 }
 
-__global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const ia_jpeg_job* __restrict__ jobs) {
+__global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const ia_jpeg_job* __restrict__ jobs,
+                                                                          int32_t* __restrict__ status) {
   const ia_jpeg_job& J = jobs[blockIdx.y];
   const uint32_t n = scan_bytes(J);
   const uint32_t tile = blockIdx.x;
@@ -226,6 +227,10 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
     if (keep_mask >> k & 1u) s_tile[local++] = b[k + 1];
     if (bnd_mask >> k & 1u) {
       if (bpos < seg_cap) seg[2 + bpos] = tile_base + local;  // the next segment starts at this clean byte
+      // RSTn markers count modulo 8.  libjpeg resynchronises by these numbers
+      // (jpeg_resync_to_restart: it may skip a marker or zero an interval); this decoder goes by
+      // position only, so a marker out of sequence means different pixels: flag the image.
+      if ((b[k + 1] & 7u) != (bpos & 7u)) atomicOr(status + blockIdx.y, 1);
       ++bpos;
     }
   }

@@ -343,6 +343,27 @@ def test_bit_errors_inside_restart_segments_decode_like_libjpeg(M):
         assert np.array_equal(got.cpu().numpy(), want), n
 
 
+def test_scan_fuzz_contract(M):
+    """scripts/jpeg_scan_fuzz.py: eleven classes of damage to the entropy-coded bytes and to the
+    restart markers.  Across all of them: cv2 returns None exactly when status bit 1 is set, and
+    status 0 means cv2's pixels.  Where only data bytes are hit the pixels are cv2's anyway;
+    damage to the markers themselves (libjpeg resynchronises by their numbers) is flagged."""
+    import importlib.util
+    from pathlib import Path
+
+    spec = importlib.util.spec_from_file_location(
+        "jpeg_scan_fuzz", Path(__file__).resolve().parent.parent / "scripts" / "jpeg_scan_fuzz.py")
+    fuzz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fuzz)
+    table = fuzz.run(per_class=60, seed=5, verbose=False)
+    assert set(table) == set(fuzz.KINDS)
+    for kind, row in table.items():
+        assert row["verdict_differs"] == 0 and row["differs_unflagged"] == 0, (kind, row)
+    assert table["cut"]["refused"] == 60 and table["cut+eoi"]["same_pixels"] == 60
+    for kind in ("byte", "bit"):
+        assert table[kind]["same_pixels"] >= 54, table[kind]
+
+
 def _strip_dht(data):
     out, i = bytearray(data[:2]), 2
     while True:
