@@ -324,7 +324,7 @@ static inline size_t round256(size_t v) { return (v + 255) & ~(size_t)255; }
 static Carve sizes(const ia_jpeg_job& j) {
   Carve c{};
   c.clean = round256((size_t)scan_bytes(j) + kCleanPad);
-  c.segment = round256(((size_t)j.num_segments + 4) * sizeof(uint32_t));
+  c.segment = round256((2 * (size_t)j.num_segments + 4) * sizeof(uint32_t));  // + one marker code per region
   c.tile = round256((size_t)tile_capacity(j) * kTileWords * sizeof(uint32_t));
   c.coef = round256((size_t)j.total_blocks * 64 * sizeof(int16_t));
   c.chain = round256((size_t)chunk_capacity(j) * kChainWords * sizeof(uint32_t));
@@ -411,8 +411,10 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
   IA_RETURN_IF(n > 65535, IA_ERR_UNSUPPORTED);
   uint32_t max_tiles = 1, max_chunks = 1;
   int max_blocks = 0, max_w = 0, max_h = 0;
+  bool any_restart = false;
   for (int i = 0; i < n; ++i) {
     const ia_jpeg_job& j = jobs_host[i];
+    any_restart |= j.restart_interval != 0;
     IA_RETURN_IF(!j.coef_dev || !j.clean_dev || !j.out_dev || !j.file_dev || !j.ticket_dev, IA_ERR_INVALID_ARGUMENT);
     max_tiles = tile_capacity(j) > max_tiles ? tile_capacity(j) : max_tiles;
     max_chunks = chunk_capacity(j) > max_chunks ? chunk_capacity(j) : max_chunks;
@@ -432,6 +434,11 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
   unstuff_scatter_kernel<<<dim3(max_tiles, n), kUnstuffThreads, 0, stream>>>(jobs_dev, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
+  if (any_restart) {  // does nothing for images whose restart markers are in sequence
+    resync_walk_kernel<<<n, 32, 0, stream>>>(jobs_dev, status_dev);
+    rc = launch_status();
+    if (rc != IA_OK) return rc;
+  }
   huffman_kernel<<<max_chunks * (unsigned)n, kHuffThreads, 0, stream>>>(
       jobs_dev, (int)max_chunks, jobs_host[0].ticket_dev, status_dev);
   rc = launch_status();

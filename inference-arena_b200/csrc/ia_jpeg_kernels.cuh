@@ -80,11 +80,17 @@ __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32
     const uint32_t r = r0 + k;
     const uint8_t prev = b[k], cur = b[k + 1], next = b[k + 2];
     if (r < n) {
+      // With a restart interval two kinds of marker do not end the data for good: RSTn, and codes
+      // below C0, which libjpeg's resynchronisation skips as garbage at the next restart
+      // (jpeg_resync_to_restart).  Both cut the stream into regions; resync_walk_kernel decides
+      // which region is which restart segment.
       if (cur == 0xFF) {
         if (next == 0x00) keep_mask |= 1u << k;
-        else if (next != 0xFF && !(rst_restarts && next >= 0xD0 && next <= 0xD7)) my_end = min(my_end, r);
+        else if (next != 0xFF && !(rst_restarts && ((next >= 0xD0 && next <= 0xD7) || next < 0xC0)))
+          my_end = min(my_end, r);
       } else if (prev == 0xFF) {
-        if (rst_restarts && cur >= 0xD0 && cur <= 0xD7) bnd_mask |= 1u << k;  // cur == 0 is stuffing: dropped
+        if (rst_restarts && ((cur >= 0xD0 && cur <= 0xD7) || (cur != 0 && cur < 0xC0)))
+          bnd_mask |= 1u << k;  // cur == 0 is stuffing: dropped
       } else {
         keep_mask |= 1u << k;
       }
@@ -226,11 +232,15 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
   for (int k = 0; k < kUnstuffPerThread; ++k) {
     if (keep_mask >> k & 1u) s_tile[local++] = b[k + 1];
     if (bnd_mask >> k & 1u) {
-      if (bpos < seg_cap) seg[2 + bpos] = tile_base + local;  // the next segment starts at this clean byte
-      // RSTn markers count modulo 8.  libjpeg resynchronises by these numbers
-      // (jpeg_resync_to_restart: it may skip a marker or zero an interval); this decoder goes by
-      // position only, so a marker out of sequence means different pixels: flag the image.
-      if ((b[k + 1] & 7u) != (bpos & 7u)) atomicOr(status + blockIdx.y, 1);
+      // RSTn markers count modulo 8 and libjpeg resynchronises by these numbers.  Keep the code of
+      // every marker (8 = a garbage code below C0); one out of sequence flags the image and makes
+      // resync_walk_kernel work out which region belongs to which segment.
+      const uint32_t code = (b[k + 1] >= 0xD0 && b[k + 1] <= 0xD7) ? (b[k + 1] & 7u) : 8u;
+      if (bpos < seg_cap) {
+        seg[2 + bpos] = tile_base + local;  // the next region starts at this clean byte
+        seg[3 + seg_cap + bpos] = code;
+      }
+      if (code != (bpos & 7u)) atomicOr(status + blockIdx.y, 1);
       ++bpos;
     }
   }
@@ -238,6 +248,41 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
   uint8_t* __restrict__ clean = J.clean_dev + tile_base;
   const uint32_t kept = total & 0xffffu;
   for (uint32_t i = threadIdx.x; i < kept; i += kUnstuffThreads) clean[i] = s_tile[i];
+}
+
+// Damaged restart markers only (flagged images; intact ones leave at once).  libjpeg restarts by
+// MCU count and takes whatever marker comes next in the stream (jdmarker.c read_restart_marker /
+// jpeg_resync_to_restart): the expected number is consumed; one or two ahead is left pending
+// (that interval gets no data and the marker is looked at again at the next restart); one or
+// two behind and garbage codes are skipped together with the data that follows them; anything
+// else is taken as the expected one.  One thread walks the marker list and turns each code
+// [3 + S + r] into the restart segment that region r + 1 (the data after marker r) belongs
+// to, or -1 for data libjpeg never decodes.  The last non-RST marker (>= C0) stays pending for good.
+__global__ void __launch_bounds__(32) resync_walk_kernel(const ia_jpeg_job* __restrict__ jobs,
+                                                          const int32_t* __restrict__ status) {
+  const ia_jpeg_job& J = jobs[blockIdx.x];
+  if (threadIdx.x != 0) return;
+  uint32_t* flags = J.segment_dev + 2 + J.num_segments;
+  if (status[blockIdx.x] == 0 || J.restart_interval == 0) return;
+  const int m = (int)J.segment_dev[1], segments = J.num_segments;
+  int32_t* code = reinterpret_cast<int32_t*>(J.segment_dev + 3 + J.num_segments);
+  int c = 0;  // next unread marker
+  for (int k = 1; k < segments; ++k) {
+    const int desired = (k - 1) & 7;
+    while (c < m) {
+      const int v = code[c];
+      const int ahead = (v - desired) & 7;
+      if (v == desired || (v < 8 && ahead != 1 && ahead != 2 && ahead != 7 && ahead != 6)) {
+        code[c++] = k;  // consumed: the data behind it is segment k
+        break;
+      }
+      if (v < 8 && (ahead == 1 || ahead == 2)) break;  // left pending: segment k gets no data
+      code[c++] = -1;  // skipped, with the data behind it
+    }
+    if (c >= m) break;  // the marker that ends the scan stays pending: no more data for anyone
+  }
+  for (; c < m; ++c) code[c] = -1;
+  *flags |= 2u;  // the Huffman kernel maps regions through the table
 }
 
 // ================================================================================ Huffman
@@ -305,7 +350,12 @@ struct Stream {
   int num_bounds;
   int bpm;
   int seg_blocks;    // blocks per restart segment (0 without restart intervals)
+  int segments;      // restart segments of the frame
   int32_t* damaged;  // status word of the image: the write pass ORs 1 into it
+  const int32_t* seg_of;  // damaged markers only (resync_walk_kernel): segment of the region behind marker r, or -1
+
+  // restart segment that region r (the data between marker r - 1 and marker r) belongs to
+  __device__ __forceinline__ int segment_of(int r) const { return r == 0 ? 0 : (seg_of ? seg_of[r - 1] : r); }
 };
 
 __device__ __forceinline__ uint32_t load_be(const uint32_t* __restrict__ words, uint32_t i) {
@@ -361,6 +411,32 @@ __device__ __noinline__ void conceal(const Stream& S, const HuffTables& T, TailS
   }
 }
 
+// Write pass, cold: the decoder leaves region r (the marker that ends it sits at bit end_pos) in
+// state (b, z) with `blk` the next block it would write.  Unless the region held exactly its
+// segment's blocks and the next region is the next segment, the image is damaged and libjpeg's
+// concealment applies: a segment that ran dry is finished from zero bits; after one that did not,
+// a following segment without data (its marker missing, or left pending by the resynchronisation)
+// still decodes its first MCU from zero bits before libjpeg notices — the rest stays zero.
+__device__ __noinline__ void leave_region(const Stream& S, const HuffTables& T, int r, int b, int z, int blk, int dc0,
+                                          int dc1, int dc2, uint32_t p, uint32_t end_pos, int total_blocks,
+                                          int16_t* __restrict__ coef) {
+  const int s = S.segment_of(r);
+  if (s < 0) return;  // data libjpeg never decodes
+  const int seg_end = min(total_blocks, (s + 1) * S.seg_blocks);
+  int next = r + 1;  // the next region that is decoded at all
+  while (next <= S.num_bounds && S.segment_of(next) < 0) ++next;
+  const int next_seg = next <= S.num_bounds ? S.segment_of(next) : S.segments;
+  if (z == 0 && b == 0 && blk == seg_end && next_seg == s + 1 && next == r + 1) return;  // intact
+  atomicOr(S.damaged, 1);
+  if (blk < seg_end) {
+    TailState ts = {b, z, blk, dc0, dc1, dc2};
+    conceal(S, T, ts, p, end_pos, seg_end, s, coef);
+  } else if (next_seg > s + 1 && seg_end < total_blocks) {
+    TailState ts = {0, 0, seg_end, 0, 0, 0};
+    conceal(S, T, ts, end_pos, end_pos, min(total_blocks, seg_end + S.seg_blocks), s + 1, coef);
+  }
+}
+
 // Decode from state (p, b, z) while p < end_bit.  kWrite: store coefficients with the DC
 // predictors in agg.d*, `since` = blocks completed since the last restart boundary before p
 // (a segment's blocks start at segment index x blocks per interval, as libjpeg restarts by MCU
@@ -381,14 +457,11 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
   int j = lo;
   int dc0 = agg.d0, dc1 = agg.d1, dc2 = agg.d2;
   if (j > 0 && __ldg(S.bounds + j - 1) * 8u == p) {
-    if (kWrite && S.seg_blocks && (z != 0 || b != 0 || (since != 0 && since != S.seg_blocks))) {
+    if (kWrite && S.seg_blocks && !(since == 0 && b == 0 && z == 0)) {
       // the predecessor stopped exactly here without stepping over the boundary (it would have
-      // handed over a count of 0), and the segment that ends here is damaged
-      atomicOr(S.damaged, 1);
-      if (since < S.seg_blocks) {
-        TailState ts = {b, z, (j - 1) * S.seg_blocks + since, dc0, dc1, dc2};
-        conceal(S, T, ts, p, p, min(total_blocks, j * S.seg_blocks), j - 1, coef);
-      }
+      // handed over a count of 0): the region that ends here is looked after from this side
+      const int sp = S.segment_of(j - 1);
+      leave_region(S, T, j - 1, b, z, sp * S.seg_blocks + since, dc0, dc1, dc2, p, p, total_blocks, coef);
     }
     b = 0, z = 0, agg.flag = 1;
     dc0 = dc1 = dc2 = 0;
@@ -398,9 +471,12 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
   const uint32_t limit = min(end_bit, S.total_bits);
   uint32_t stop = min(S.total_bits, next_bound);  // no symbol may cross this bit
   uint32_t info = T.blk_info[b];                  // component | DC slot << 8 | AC slot << 16
-  // segment j owns blocks [j * seg_blocks, seg_end); what a damaged segment decodes beyond is dropped
-  int blk = j * S.seg_blocks + since;
-  int seg_end = S.seg_blocks ? min(total_blocks, (j + 1) * S.seg_blocks) : total_blocks;
+  // Region j is restart segment s (s = j unless markers are damaged; -1: data libjpeg never
+  // decodes, nothing is written).  Segment s owns blocks [s * seg_blocks, seg_end); what a
+  // damaged segment decodes beyond them is dropped.
+  int s = kWrite ? S.segment_of(j) : 0;
+  int blk = s < 0 ? 0 : s * S.seg_blocks + since;
+  int seg_end = s < 0 ? 0 : (S.seg_blocks ? min(total_blocks, (s + 1) * S.seg_blocks) : total_blocks);
   int16_t* blk_ptr = kWrite ? coef + (size_t)blk * 64 : nullptr;
   int nb = 0;
   uint32_t tail_from = 0xffffffffu;  // write pass: where the data ran out inside a symbol
@@ -433,16 +509,13 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
       }
       // ran into the padding before a restart marker: new segment
       if (kWrite) {
-        const int next_first = (j + 1) * S.seg_blocks;
-        if (z != 0 || b != 0 || blk != next_first) {  // too few or too many blocks: a damaged segment
-          atomicOr(S.damaged, 1);
-          if (blk < seg_end) {
-            TailState ts = {b, z, blk, dc0, dc1, dc2};
-            conceal(S, T, ts, p, next_bound, seg_end, j, coef);
-          }
-        }
-        blk = next_first, blk_ptr = coef + (size_t)blk * 64;
-        seg_end = min(total_blocks, next_first + S.seg_blocks);
+        // too few or too many blocks, or markers that are not what they should be: concealment
+        if (z != 0 || b != 0 || blk != seg_end || S.seg_of)
+          leave_region(S, T, j, b, z, blk, dc0, dc1, dc2, p, next_bound, total_blocks, coef);
+        s = S.segment_of(j + 1);
+        blk = s < 0 ? 0 : s * S.seg_blocks;
+        seg_end = s < 0 ? 0 : min(total_blocks, blk + S.seg_blocks);
+        blk_ptr = coef + (size_t)blk * 64;
       }
       nb = 0;  // blocks are counted from the last boundary
       p = next_bound, b = 0, z = 0, agg.flag = 1;
@@ -495,13 +568,13 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
     // one thread owns the end: the one that decoded up to it (the first one if there is no data)
     const bool owns_end = p_io < S.total_bits || (S.total_bits == 0 && end_bit == (uint32_t)kSubseqBits);
     if (tail_from == 0xffffffffu && p == S.total_bits && end_bit >= S.total_bits) tail_from = p;
-    if (owns_end && tail_from != 0xffffffffu && stop == S.total_bits && blk < total_blocks) {
+    if (owns_end && s >= 0 && tail_from != 0xffffffffu && stop == S.total_bits && blk < total_blocks) {
       // (beyond this segment's blocks too when the data ended at or after its last MCU and the
       // restart that is due has no marker: one more MCU from zeros, predictors reset)
       TailState ts = {b, z, blk, dc0, dc1, dc2};
       uint32_t q = tail_from;
       if (blk >= seg_end) ts = {0, 0, seg_end, 0, 0, 0}, q = S.total_bits;  // what a damaged segment had beyond its blocks is skipped
-      if (ts.blk < total_blocks) conceal(S, T, ts, q, S.total_bits, total_blocks, j, coef);
+      if (ts.blk < total_blocks) conceal(S, T, ts, q, S.total_bits, total_blocks, s, coef);
       p = S.total_bits;
     }
   }
@@ -594,7 +667,11 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
   S.num_bounds = (int)J.segment_dev[1];
   S.bpm = J.blocks_per_mcu;
   S.seg_blocks = J.restart_interval * J.blocks_per_mcu;
+  S.segments = J.num_segments;
   S.damaged = status + image;
+  S.seg_of = (J.segment_dev[2 + J.num_segments] & 2u)
+                 ? reinterpret_cast<const int32_t*>(J.segment_dev + 3 + J.num_segments)
+                 : nullptr;
   const int num_chunks = S.total_bits ? (int)((S.total_bits + kChunkBits - 1) / kChunkBits) : 1;
   if (chunk >= num_chunks) return;  // nothing waits on the spare CTAs of shorter images
   build_tables(J, T);
