@@ -297,8 +297,9 @@ typedef struct ia_jpeg_job {
   const uint8_t* file_dev; /* the whole file; read in aligned 16-byte units, so the bytes up to the next
                               16-byte boundary after its end must be readable (any cudaMalloc'ed buffer is) */
   uint8_t* clean_dev;      /* entropy-coded bytes without stuffing / RST markers */
-  uint32_t* segment_dev;   /* [0] clean bytes, [1] restart boundaries found, [2..] their clean byte offsets,
-                              [2 + num_segments] 1 = no marker behind the entropy-coded data */
+  uint32_t* segment_dev;   /* [0] clean bytes, [1] markers found inside the data, [2] flags (1 = no marker
+                              behind the data), [3..] clean byte offsets of the regions between the
+                              markers, then one marker code / restart segment per region */
   int16_t* coef_dev;       /* [total_blocks, 64] natural order, DC absolute, not dequantised */
   uint8_t* plane_dev[IA_JPEG_MAX_COMPONENTS]; /* per component, padded to whole MCUs */
   uint8_t* out_dev;        /* uint8 [out_height, out_width, 3] RGB */
@@ -325,8 +326,9 @@ int ia_jpeg_plan(ia_jpeg_job* jobs_host, int n, const uint8_t* const* file_dev,
                  uint8_t* const* out_dev, void* workspace_dev, size_t workspace_bytes);
 /* jobs_dev: the planned job array copied to device memory by the caller (jobs_host is read
  * for launch geometry only).  status_dev int32 [n]: 0 = the pixels are libjpeg's;
- * bit 0 = the entropy-coded data held fewer or more blocks than the frame (a damaged stream:
- * undamaged MCUs are exact, the rest differs from libjpeg's error concealment);
+ * bit 0 = a damaged stream (too few or too many blocks, restart markers out of place): it is
+ * decoded and concealed the way libjpeg does it — cv2.imdecode warns "Corrupt JPEG data" and
+ * returns these very pixels;
  * bit 1 = in addition the data simply ends, without a marker behind it, before the last
  * block — there libjpeg runs out of input, cv2.imdecode returns None and the reference
  * raises "Failed to decode image from bytes" (shared/processing/jpeg.py raises it too). */

@@ -324,7 +324,7 @@ static inline size_t round256(size_t v) { return (v + 255) & ~(size_t)255; }
 static Carve sizes(const ia_jpeg_job& j) {
   Carve c{};
   c.clean = round256((size_t)scan_bytes(j) + kCleanPad);
-  c.segment = round256((2 * (size_t)j.num_segments + 4) * sizeof(uint32_t));  // + one marker code per region
+  c.segment = round256((3 + 2 * (size_t)region_capacity(j)) * sizeof(uint32_t));  // header, offsets, marker codes
   c.tile = round256((size_t)tile_capacity(j) * kTileWords * sizeof(uint32_t));
   c.coef = round256((size_t)j.total_blocks * 64 * sizeof(int16_t));
   c.chain = round256((size_t)chunk_capacity(j) * kChainWords * sizeof(uint32_t));

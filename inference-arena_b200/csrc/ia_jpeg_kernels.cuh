@@ -35,6 +35,12 @@ __host__ __device__ inline uint32_t scan_bytes(const ia_jpeg_job& j) { return j.
 __host__ __device__ inline uint32_t tile_capacity(const ia_jpeg_job& j) {
   return (scan_bytes(j) + kTileBytes - 1) / kTileBytes + 1;
 }
+// ia_jpeg_job::segment_dev: [0] clean bytes, [1] markers recorded, [2] flags (1 = no marker behind
+// the data, 2 = the region table below holds segments), [3, 3 + cap) clean byte offset at which
+// the region behind marker r starts, [3 + cap, 3 + 2 cap) that marker's code, later the restart
+// segment of the region.  A damaged stream can hold more markers than segments; beyond cap they
+// are not told apart any more (the image is flagged long before).
+__host__ __device__ inline uint32_t region_capacity(const ia_jpeg_job& j) { return 2u * (uint32_t)j.num_segments + 8u; }
 __host__ __device__ inline uint32_t chunk_capacity(const ia_jpeg_job& j) {
   return (scan_bytes(j) + kChunkBytes - 1) / kChunkBytes + 1;
 }
@@ -192,10 +198,10 @@ __global__ void __launch_bounds__(32) unstuff_scan_kernel(const ia_jpeg_job* __r
   for (int i = lane; i < kCleanPad; i += 32) J.clean_dev[base_keep + i] = 0;
   if (lane == 0) {
     J.segment_dev[0] = base_keep;
-    J.segment_dev[1] = min(base_bnd, (uint32_t)J.num_segments);
+    J.segment_dev[1] = min(base_bnd, region_capacity(J));
     // no marker behind the entropy-coded bytes (or a lone FF as the last byte): libjpeg would
     // run out of input if the blocks are not all there
-    J.segment_dev[2 + J.num_segments] = scan_end == 0xffffffffu || scan_end + 1 >= scan_bytes(J);
+    J.segment_dev[2] = scan_end == 0xffffffffu || scan_end + 1 >= scan_bytes(J);
     // the Huffman kernel ORs its findings in; a restart marker count other than the interval
     // implies is damage already (without an interval libjpeg stops reading at the first one)
     status[blockIdx.x] = base_bnd + 1 == (uint32_t)J.num_segments ? 0 : 1;
@@ -227,7 +233,7 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
   uint32_t local = excl & 0xffffu;
   uint32_t bpos = rec[1] + (excl >> 16);
   uint32_t* __restrict__ seg = J.segment_dev;
-  const uint32_t seg_cap = (uint32_t)J.num_segments;
+  const uint32_t seg_cap = region_capacity(J);
 #pragma unroll
   for (int k = 0; k < kUnstuffPerThread; ++k) {
     if (keep_mask >> k & 1u) s_tile[local++] = b[k + 1];
@@ -237,7 +243,7 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
       // resync_walk_kernel work out which region belongs to which segment.
       const uint32_t code = (b[k + 1] >= 0xD0 && b[k + 1] <= 0xD7) ? (b[k + 1] & 7u) : 8u;
       if (bpos < seg_cap) {
-        seg[2 + bpos] = tile_base + local;  // the next region starts at this clean byte
+        seg[3 + bpos] = tile_base + local;  // the next region starts at this clean byte
         seg[3 + seg_cap + bpos] = code;
       }
       if (code != (bpos & 7u)) atomicOr(status + blockIdx.y, 1);
@@ -256,16 +262,16 @@ __global__ void __launch_bounds__(kUnstuffThreads) unstuff_scatter_kernel(const 
 // (that interval gets no data and the marker is looked at again at the next restart); one or
 // two behind and garbage codes are skipped together with the data that follows them; anything
 // else is taken as the expected one.  One thread walks the marker list and turns each code
-// [3 + S + r] into the restart segment that region r + 1 (the data after marker r) belongs
+// (second table of segment_dev) into the restart segment that the data after that marker belongs
 // to, or -1 for data libjpeg never decodes.  The last non-RST marker (>= C0) stays pending for good.
 __global__ void __launch_bounds__(32) resync_walk_kernel(const ia_jpeg_job* __restrict__ jobs,
                                                           const int32_t* __restrict__ status) {
   const ia_jpeg_job& J = jobs[blockIdx.x];
   if (threadIdx.x != 0) return;
-  uint32_t* flags = J.segment_dev + 2 + J.num_segments;
+  uint32_t* flags = J.segment_dev + 2;
   if (status[blockIdx.x] == 0 || J.restart_interval == 0) return;
   const int m = (int)J.segment_dev[1], segments = J.num_segments;
-  int32_t* code = reinterpret_cast<int32_t*>(J.segment_dev + 3 + J.num_segments);
+  int32_t* code = reinterpret_cast<int32_t*>(J.segment_dev + 3 + region_capacity(J));
   int c = 0;  // next unread marker
   for (int k = 1; k < segments; ++k) {
     const int desired = (k - 1) & 7;
@@ -457,11 +463,15 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
   int j = lo;
   int dc0 = agg.d0, dc1 = agg.d1, dc2 = agg.d2;
   if (j > 0 && __ldg(S.bounds + j - 1) * 8u == p) {
-    if (kWrite && S.seg_blocks && !(since == 0 && b == 0 && z == 0)) {
+    if (kWrite && S.seg_blocks && (!(since == 0 && b == 0 && z == 0) || p == 0)) {
       // the predecessor stopped exactly here without stepping over the boundary (it would have
-      // handed over a count of 0): the region that ends here is looked after from this side
-      const int sp = S.segment_of(j - 1);
-      leave_region(S, T, j - 1, b, z, sp * S.seg_blocks + since, dc0, dc1, dc2, p, p, total_blocks, coef);
+      // handed over a count of 0) — or there is none, the scan begins with a marker: the region
+      // that ends here is looked after from this side
+      int j0 = j - 1;  // several markers in a row: the regions between them are empty
+      while (j0 > 0 && __ldg(S.bounds + j0 - 1) * 8u == p) --j0;
+      leave_region(S, T, j0, b, z, S.segment_of(j0) * S.seg_blocks + since, dc0, dc1, dc2, p, p, total_blocks, coef);
+      for (int e = j0 + 1; e < j; ++e)
+        leave_region(S, T, e, 0, 0, S.segment_of(e) * S.seg_blocks, 0, 0, 0, p, p, total_blocks, coef);
     }
     b = 0, z = 0, agg.flag = 1;
     dc0 = dc1 = dc2 = 0;
@@ -491,6 +501,10 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
   // The body has no data-dependent branches apart from the rare cases (a code longer than the
   // look-up, a restart boundary, the end of the stream, the end of a block): the 32 lanes of a
   // warp sit at unrelated places of their blocks, and every divergent path is paid by all.
+  // (Stepping over a restart boundary happens outside the symbol loop: it may call the cold
+  // concealment code, and a call inside the loop costs the loop its registers.)
+  for (;;) {
+  bool crossing = false;
   while (p < limit) {
     const uint32_t bits = __funnelshift_l(w1, w0, p);
     const bool dc_mode = z == 0;
@@ -507,25 +521,8 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
         p = S.total_bits;
         break;
       }
-      // ran into the padding before a restart marker: new segment
-      if (kWrite) {
-        // too few or too many blocks, or markers that are not what they should be: concealment
-        if (z != 0 || b != 0 || blk != seg_end || S.seg_of)
-          leave_region(S, T, j, b, z, blk, dc0, dc1, dc2, p, next_bound, total_blocks, coef);
-        s = S.segment_of(j + 1);
-        blk = s < 0 ? 0 : s * S.seg_blocks;
-        seg_end = s < 0 ? 0 : min(total_blocks, blk + S.seg_blocks);
-        blk_ptr = coef + (size_t)blk * 64;
-      }
-      nb = 0;  // blocks are counted from the last boundary
-      p = next_bound, b = 0, z = 0, agg.flag = 1;
-      dc0 = dc1 = dc2 = 0;
-      ++j;
-      next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
-      stop = min(S.total_bits, next_bound);
-      info = T.blk_info[0];
-      if (p < limit) reload();
-      continue;
+      crossing = true;  // ran into the padding before a restart marker: new segment
+      break;
     }
     // EXTEND (T.81 F.2.2.1): magnitude bits with a leading 0 mean value - (2^s - 1); s = 0 gives 0
     const uint32_t tail = bits << len;
@@ -559,6 +556,36 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
       info = T.blk_info[b];
     }
   }
+  if (!crossing) break;
+    {  // step over the boundary into the next region
+      if (kWrite) {
+        // too few or too many blocks, or markers that are not what they should be: concealment
+        if (z != 0 || b != 0 || blk != seg_end || S.seg_of)
+          leave_region(S, T, j, b, z, blk, dc0, dc1, dc2, p, next_bound, total_blocks, coef);
+        s = S.segment_of(j + 1);
+        blk = s < 0 ? 0 : s * S.seg_blocks;
+        seg_end = s < 0 ? 0 : min(total_blocks, blk + S.seg_blocks);
+        blk_ptr = coef + (size_t)blk * 64;
+      }
+      nb = 0;  // blocks are counted from the last boundary
+      p = next_bound, b = 0, z = 0, agg.flag = 1;
+      dc0 = dc1 = dc2 = 0;
+      ++j;
+      next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
+      while (kWrite && next_bound == p) {  // two markers in a row: an empty region, left at once
+        leave_region(S, T, j, 0, 0, blk, 0, 0, 0, p, p, total_blocks, coef);
+        ++j;
+        s = S.segment_of(j);
+        blk = s < 0 ? 0 : s * S.seg_blocks;
+        seg_end = s < 0 ? 0 : min(total_blocks, blk + S.seg_blocks);
+        blk_ptr = coef + (size_t)blk * 64;
+        next_bound = j < S.num_bounds ? __ldg(S.bounds + j) * 8u : 0xffffffffu;
+      }
+      stop = min(S.total_bits, next_bound);
+      info = T.blk_info[0];
+      if (p < limit) reload();
+    }
+  }
   if (kWrite) {
     // Blocks are missing and the data is over (a file cut short and closed by a marker; intact
     // restart segments before it): libjpeg supplies zero bits, finishes the MCU in hand from
@@ -568,7 +595,7 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
     // one thread owns the end: the one that decoded up to it (the first one if there is no data)
     const bool owns_end = p_io < S.total_bits || (S.total_bits == 0 && end_bit == (uint32_t)kSubseqBits);
     if (tail_from == 0xffffffffu && p == S.total_bits && end_bit >= S.total_bits) tail_from = p;
-    if (owns_end && s >= 0 && tail_from != 0xffffffffu && stop == S.total_bits && blk < total_blocks) {
+    if (owns_end && s >= 0 && tail_from != 0xffffffffu && stop == S.total_bits && min(blk, seg_end) < total_blocks) {
       // (beyond this segment's blocks too when the data ended at or after its last MCU and the
       // restart that is due has no marker: one more MCU from zeros, predictors reset)
       TailState ts = {b, z, blk, dc0, dc1, dc2};
@@ -663,14 +690,14 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
   Stream S;
   S.words = reinterpret_cast<const uint32_t*>(J.clean_dev);
   S.total_bits = J.segment_dev[0] * 8u;
-  S.bounds = J.segment_dev + 2;
+  S.bounds = J.segment_dev + 3;
   S.num_bounds = (int)J.segment_dev[1];
   S.bpm = J.blocks_per_mcu;
   S.seg_blocks = J.restart_interval * J.blocks_per_mcu;
   S.segments = J.num_segments;
   S.damaged = status + image;
-  S.seg_of = (J.segment_dev[2 + J.num_segments] & 2u)
-                 ? reinterpret_cast<const int32_t*>(J.segment_dev + 3 + J.num_segments)
+  S.seg_of = (J.segment_dev[2] & 2u)
+                 ? reinterpret_cast<const int32_t*>(J.segment_dev + 3 + region_capacity(J))
                  : nullptr;
   const int num_chunks = S.total_bits ? (int)((S.total_bits + kChunkBits - 1) / kChunkBits) : 1;
   if (chunk >= num_chunks) return;  // nothing waits on the spare CTAs of shorter images
@@ -907,7 +934,7 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
       // the write pass steps over their boundaries)
       const int want_nb = J.total_blocks - S.num_bounds * S.seg_blocks;
       int st = out.nb == want_nb ? 0 : 1;
-      if (out.nb < want_nb && (J.segment_dev[2 + J.num_segments] & 1u)) st |= 2;
+      if (out.nb < want_nb && (J.segment_dev[2] & 1u)) st |= 2;
       if (st) atomicOr(status + image, st);
     }
   }

@@ -79,7 +79,7 @@ KINDS = ("byte", "bit", "ff", "delete", "insert", "cut+eoi", "cut",
          "rst renumber", "rst remove", "rst duplicate", "rst insert")
 
 
-def run(per_class=150, seed=1, verbose=True):
+def run(per_class=150, seed=1, verbose=True, dump=None):
     rng = np.random.default_rng(seed)
     files = bases()
     table = {}
@@ -96,7 +96,7 @@ def run(per_class=150, seed=1, verbose=True):
         status = batch.status.cpu().tolist()
         row = dict(n=len(blobs), cv2_decodes=0, same_pixels=0, flagged=0, differs_unflagged=0, cv2_fails=0, refused=0,
                    verdict_differs=0)
-        for ref, st, got in zip(refs, status, batch.frames):
+        for blob, ref, st, got in zip(blobs, refs, status, batch.frames):
             refused = bool(st & 2)
             if ref is None:
                 row["cv2_fails"] += 1
@@ -108,6 +108,8 @@ def run(per_class=150, seed=1, verbose=True):
             row["flagged"] += st != 0
             same = np.array_equal(got.cpu().numpy(), ref[..., ::-1])
             row["same_pixels"] += same
+            if not same and dump is not None:
+                dump.append((kind, blob))
             row["differs_unflagged"] += (not same) and st == 0  # must stay 0: status 0 promises cv2's pixels
         table[kind] = row
         if verbose:
@@ -116,4 +118,9 @@ def run(per_class=150, seed=1, verbose=True):
 
 
 if __name__ == "__main__":
-    run(int(sys.argv[1]) if len(sys.argv) > 1 else 150, int(sys.argv[2]) if len(sys.argv) > 2 else 1)
+    differing = []
+    run(int(sys.argv[1]) if len(sys.argv) > 1 else 150, int(sys.argv[2]) if len(sys.argv) > 2 else 1, dump=differing)
+    out = REPO / "gpurun_out"
+    out.mkdir(exist_ok=True)
+    for i, (kind, blob) in enumerate(differing[:40]):  # for a look with the oracle on the CPU
+        (out / f"scanfuzz_{i:02d}_{kind.replace(' ', '_').replace('+', '_')}.jpg").write_bytes(blob)

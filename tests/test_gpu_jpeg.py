@@ -346,8 +346,7 @@ def test_bit_errors_inside_restart_segments_decode_like_libjpeg(M):
 def test_scan_fuzz_contract(M):
     """scripts/jpeg_scan_fuzz.py: eleven classes of damage to the entropy-coded bytes and to the
     restart markers.  Across all of them: cv2 returns None exactly when status bit 1 is set, and
-    status 0 means cv2's pixels.  Where only data bytes are hit the pixels are cv2's anyway;
-    damage to the markers themselves (libjpeg resynchronises by their numbers) is flagged."""
+    every file cv2 decodes comes back with cv2's pixels, flagged (status 1) when damaged."""
     import importlib.util
     from pathlib import Path
 
@@ -359,9 +358,11 @@ def test_scan_fuzz_contract(M):
     assert set(table) == set(fuzz.KINDS)
     for kind, row in table.items():
         assert row["verdict_differs"] == 0 and row["differs_unflagged"] == 0, (kind, row)
+        # libjpeg's whole damage handling is reproduced: concealment of short segments, restart
+        # by MCU count, resynchronisation by marker number (jpeg_resync_to_restart)
+        assert row["same_pixels"] == row["cv2_decodes"], (kind, row)
     assert table["cut"]["refused"] == 60 and table["cut+eoi"]["same_pixels"] == 60
-    for kind in ("byte", "bit"):
-        assert table[kind]["same_pixels"] >= 54, table[kind]
+    assert sum(row["flagged"] for row in table.values()) > 300
 
 
 def _strip_dht(data):
