@@ -18,6 +18,7 @@
 //   idct: dequantise + libjpeg's jidctint.c "islow" integer IDCT, one thread per block;
 //   colour: libjpeg's fancy (triangle) chroma upsampling, jdcolor.c fixed-point YCbCr->RGB,
 //       EXIF orientation, RGB store.
+#include <stdlib.h>
 #include <string.h>
 
 #include "ia_jpeg_kernels.cuh"
@@ -439,8 +440,26 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
     rc = launch_status();
     if (rc != IA_OK) return rc;
   }
-  huffman_kernel<<<max_chunks * (unsigned)n, kHuffThreads, 0, stream>>>(
-      jobs_dev, (int)max_chunks, jobs_host[0].ticket_dev, status_dev);
+  // Thread granularity: 256 bytes per thread once the batch fills the GPU even with the larger
+  // chunks (measured cross-over, see ia_jpeg_kernels.cuh), else 128.  IA_JPEG_SUBSEQ=128|256 overrides.
+  unsigned long long chunks_large = 0;
+  uint32_t max_chunks_large = 1;
+  for (int i = 0; i < n; ++i) {
+    const uint32_t c = (scan_bytes(jobs_host[i]) + 2 * kChunkBytes - 1) / (2 * kChunkBytes) + 1;
+    chunks_large += c - 1;
+    max_chunks_large = c > max_chunks_large ? c : max_chunks_large;
+  }
+  static const int forced = [] {
+    const char* e = getenv("IA_JPEG_SUBSEQ");
+    return e ? atoi(e) : 0;
+  }();
+  const bool large = forced ? forced == kSubseqBytesLarge : chunks_large >= kLargeChunksFrom;
+  if (large)
+    huffman_kernel<kSubseqBytesLarge><<<max_chunks_large * (unsigned)n, kHuffThreads, 0, stream>>>(
+        jobs_dev, (int)max_chunks_large, jobs_host[0].ticket_dev, status_dev);
+  else
+    huffman_kernel<kSubseqBytes><<<max_chunks * (unsigned)n, kHuffThreads, 0, stream>>>(
+        jobs_dev, (int)max_chunks, jobs_host[0].ticket_dev, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
   idct_kernel<<<dim3((max_blocks + kIdctThreads - 1) / kIdctThreads, n), kIdctThreads, 0, stream>>>(jobs_dev);

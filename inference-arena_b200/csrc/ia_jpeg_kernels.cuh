@@ -17,7 +17,15 @@
 namespace ia {
 namespace jpeg {
 
+// Bytes of the clean stream per thread of huffman_kernel.  Two instantiations: 128 (64 KB chunks:
+// more CTAs per image, lowest latency for a few frames) and 256 (128 KB chunks: fewer rounds of
+// the self-synchronising decode and less repeated work, best throughput once the batch fills the
+// GPU; 64, 384 and 512 are slower on both counts).  The workspace is sized for the smaller one.
 constexpr int kSubseqBytes = 128;
+constexpr int kSubseqBytesLarge = 256;
+// 128 KB chunks in the batch from which the larger size wins (measured: 64 x 1080p 3.2 -> 2.6 ms,
+// 256 x VGA 2.13 -> 1.98 ms; 128 x VGA, 128 such chunks, 1.29 -> 1.67 ms; 32 x 1080p, 224, equal)
+constexpr unsigned long long kLargeChunksFrom = 224;
 constexpr int kSubseqBits = kSubseqBytes * 8;
 constexpr int kHuffThreads = 512;
 constexpr uint32_t kChunkBits = (uint32_t)kHuffThreads * kSubseqBits;
@@ -357,6 +365,7 @@ struct Stream {
   int bpm;
   int seg_blocks;    // blocks per restart segment (0 without restart intervals)
   int segments;      // restart segments of the frame
+  uint32_t first_end_bit;  // where the first subsequence of the stream ends
   int32_t* damaged;  // status word of the image: the write pass ORs 1 into it
   const int32_t* seg_of;  // damaged markers only (resync_walk_kernel): segment of the region behind marker r, or -1
 
@@ -593,7 +602,7 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
     // (jdhuff.c decode_mcu, insufficient_data).  The counting passes do not see these blocks,
     // so the image is still reported as damaged.
     // one thread owns the end: the one that decoded up to it (the first one if there is no data)
-    const bool owns_end = p_io < S.total_bits || (S.total_bits == 0 && end_bit == (uint32_t)kSubseqBits);
+    const bool owns_end = p_io < S.total_bits || (S.total_bits == 0 && end_bit == S.first_end_bit);
     if (tail_from == 0xffffffffu && p == S.total_bits && end_bit >= S.total_bits) tail_from = p;
     if (owns_end && s >= 0 && tail_from != 0xffffffffu && stop == S.total_bits && min(blk, seg_end) < total_blocks) {
       // (beyond this segment's blocks too when the data ended at or after its last MCU and the
@@ -663,9 +672,12 @@ __device__ __forceinline__ void build_tables(const ia_jpeg_job& J, HuffTables& T
 // predecessor's published record, repairs its first subsequences, publishes its own record and
 // only then writes coefficients.  Tickets are handed out in launch order, so the CTA a chunk
 // waits for is always already running.
+template <int kSub>
 __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_job* __restrict__ jobs, int max_chunks,
                                                                uint32_t* __restrict__ ticket_counter,
                                                                int32_t* __restrict__ status) {
+  constexpr int kSubseqBits = kSub * 8;  // this instantiation's, not the namespace's
+  constexpr uint32_t kChunkBits = (uint32_t)kHuffThreads * kSubseqBits;
   __shared__ HuffTables T;
   // per subsequence: assumed entry state, resulting exit state and contribution
   __shared__ uint32_t s_entry_p[kHuffThreads], s_entry_bz[kHuffThreads];
@@ -695,6 +707,7 @@ __global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_
   S.bpm = J.blocks_per_mcu;
   S.seg_blocks = J.restart_interval * J.blocks_per_mcu;
   S.segments = J.num_segments;
+  S.first_end_bit = (uint32_t)kSubseqBits;
   S.damaged = status + image;
   S.seg_of = (J.segment_dev[2] & 2u)
                  ? reinterpret_cast<const int32_t*>(J.segment_dev + 3 + region_capacity(J))
