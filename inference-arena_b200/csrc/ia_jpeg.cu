@@ -440,26 +440,41 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
     rc = launch_status();
     if (rc != IA_OK) return rc;
   }
-  // Thread granularity: 256 bytes per thread once the batch fills the GPU even with the larger
-  // chunks (measured cross-over, see ia_jpeg_kernels.cuh), else 128.  IA_JPEG_SUBSEQ=128|256 overrides.
-  unsigned long long chunks_large = 0;
-  uint32_t max_chunks_large = 1;
+  // Configuration of the Huffman kernel (measured cross-overs, see ia_jpeg_kernels.cuh):
+  // 256 threads x 128-byte subsequences (32 KB chunks) for a few frames, 256-byte subsequences
+  // once the batch holds enough chunks, and 512 threads x 256 bytes (128 KB chunks) for large
+  // batches of large files.  IA_JPEG_SUBSEQ=128|256 and IA_JPEG_THREADS=256|512 override.
+  unsigned long long total_bytes = 0, ctas_large_sub = 0;
+  uint32_t max_scan = 0;
   for (int i = 0; i < n; ++i) {
-    const uint32_t c = (scan_bytes(jobs_host[i]) + 2 * kChunkBytes - 1) / (2 * kChunkBytes) + 1;
-    chunks_large += c - 1;
-    max_chunks_large = c > max_chunks_large ? c : max_chunks_large;
+    const uint32_t bytes = scan_bytes(jobs_host[i]);
+    total_bytes += bytes;
+    ctas_large_sub += (bytes + kHuffThreads * kSubseqBytesLarge - 1) / (kHuffThreads * kSubseqBytesLarge);
+    max_scan = bytes > max_scan ? bytes : max_scan;
   }
-  static const int forced = [] {
-    const char* e = getenv("IA_JPEG_SUBSEQ");
-    return e ? atoi(e) : 0;
-  }();
-  const bool large = forced ? forced == kSubseqBytesLarge : chunks_large >= kLargeChunksFrom;
-  if (large)
-    huffman_kernel<kSubseqBytesLarge><<<max_chunks_large * (unsigned)n, kHuffThreads, 0, stream>>>(
-        jobs_dev, (int)max_chunks_large, jobs_host[0].ticket_dev, status_dev);
+  static const int forced_sub = [] { const char* e = getenv("IA_JPEG_SUBSEQ"); return e ? atoi(e) : 0; }();
+  static const int forced_threads = [] { const char* e = getenv("IA_JPEG_THREADS"); return e ? atoi(e) : 0; }();
+  const unsigned long long avg_bytes = total_bytes / (unsigned)n;
+  const bool large_files = avg_bytes >= kLargeFileBytes;
+  int threads = large_files && total_bytes >= kLargeBatchBytes ? kHuffThreadsLarge : kHuffThreads;
+  int sub = threads == kHuffThreadsLarge || ctas_large_sub >= kLargeSubseqCtasFrom ||
+                    (large_files && total_bytes >= kLargeSubseqBytesFrom)
+                ? kSubseqBytesLarge
+                : kSubseqBytes;
+  if (forced_threads == kHuffThreads || forced_threads == kHuffThreadsLarge) threads = forced_threads;
+  if (forced_sub == kSubseqBytes || forced_sub == kSubseqBytesLarge) sub = forced_sub;
+  const uint32_t chunk_bytes = (uint32_t)threads * (uint32_t)sub;
+  const uint32_t chunks = (max_scan + chunk_bytes - 1) / chunk_bytes + 1;
+  const unsigned grid = chunks * (unsigned)n;
+  uint32_t* ticket = jobs_host[0].ticket_dev;
+  if (threads == kHuffThreadsLarge && sub == kSubseqBytesLarge)
+    huffman_kernel<kHuffThreadsLarge, 3, kSubseqBytesLarge><<<grid, threads, 0, stream>>>(jobs_dev, (int)chunks, ticket, status_dev);
+  else if (threads == kHuffThreadsLarge)
+    huffman_kernel<kHuffThreadsLarge, 3, kSubseqBytes><<<grid, threads, 0, stream>>>(jobs_dev, (int)chunks, ticket, status_dev);
+  else if (sub == kSubseqBytesLarge)
+    huffman_kernel<kHuffThreads, 4, kSubseqBytesLarge><<<grid, threads, 0, stream>>>(jobs_dev, (int)chunks, ticket, status_dev);
   else
-    huffman_kernel<kSubseqBytes><<<max_chunks * (unsigned)n, kHuffThreads, 0, stream>>>(
-        jobs_dev, (int)max_chunks, jobs_host[0].ticket_dev, status_dev);
+    huffman_kernel<kHuffThreads, 4, kSubseqBytes><<<grid, threads, 0, stream>>>(jobs_dev, (int)chunks, ticket, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
   idct_kernel<<<dim3((max_blocks + kIdctThreads - 1) / kIdctThreads, n), kIdctThreads, 0, stream>>>(jobs_dev);

@@ -17,17 +17,28 @@
 namespace ia {
 namespace jpeg {
 
-// Bytes of the clean stream per thread of huffman_kernel.  Two instantiations: 128 (64 KB chunks:
-// more CTAs per image, lowest latency for a few frames) and 256 (128 KB chunks: fewer rounds of
-// the self-synchronising decode and less repeated work, best throughput once the batch fills the
-// GPU; 64, 384 and 512 are slower on both counts).  The workspace is sized for the smaller one.
+// Bytes of the clean stream per thread of huffman_kernel.  Two instantiations: 128 (more CTAs per
+// image, lowest latency for a few frames) and 256 (fewer rounds of the self-synchronising decode
+// and less repeated work, best throughput once the batch fills the GPU; 64, 384 and 512 are
+// slower on both counts).  The workspace is sized for the smaller one.
 constexpr int kSubseqBytes = 128;
 constexpr int kSubseqBytesLarge = 256;
-// 128 KB chunks in the batch from which the larger size wins (measured: 64 x 1080p 3.2 -> 2.6 ms,
-// 256 x VGA 2.13 -> 1.98 ms; 128 x VGA, 128 such chunks, 1.29 -> 1.67 ms; 32 x 1080p, 224, equal)
-constexpr unsigned long long kLargeChunksFrom = 224;
+// Cross-overs measured on B200 (profiles/README.md).  256-byte subsequences win once their CTAs
+// alone fill most of the GPU (256 x VGA: 1.93 -> 1.59 ms; 128 x VGA, 256 CTAs: 1.08 -> 1.26 ms),
+// and for large files — many chunks chained per image — already from a few megabytes (8 x 1080p
+// 1.03 -> 0.95 ms, one frame 0.54 -> 0.66 ms).  The 512-thread kernel wins only for big batches
+// of large files (64 x 1080p: 2.75 -> 2.63 ms; 32 x 1080p: 1.63 -> 1.83 ms).
+constexpr unsigned long long kLargeSubseqCtasFrom = 384;
+constexpr unsigned long long kLargeSubseqBytesFrom = 6ull << 20;
+constexpr unsigned long long kLargeBatchBytes = 40ull << 20;
+constexpr unsigned long long kLargeFileBytes = 256ull << 10;
 constexpr int kSubseqBits = kSubseqBytes * 8;
-constexpr int kHuffThreads = 512;
+// huffman_kernel comes as 256 threads x 4 CTAs per SM (64 registers, no spills: best latency and
+// best for small files) and as 512 threads x 3 CTAs (42 registers; with 256-byte subsequences its
+// 128 KB chunks are best for batches of large files).  The constants here are the smallest
+// configuration: they size the workspace.
+constexpr int kHuffThreads = 256;
+constexpr int kHuffThreadsLarge = 512;
 constexpr uint32_t kChunkBits = (uint32_t)kHuffThreads * kSubseqBits;
 constexpr uint32_t kChunkBytes = kChunkBits / 8;
 constexpr int kLutBits = 10;
@@ -624,8 +635,8 @@ __device__ __forceinline__ void decode_range(const Stream& S, const HuffTables& 
 // a table get identical copies: simpler than a mapping, and the copies are built in parallel.)
 __device__ __forceinline__ void build_tables(const ia_jpeg_job& J, HuffTables& T) {
   const int tid = threadIdx.x;
-  for (int i = tid; i < kHuffSlots * (1 << kLutBits); i += kHuffThreads) (&T.lut[0][0])[i] = 0;
-  for (int i = tid; i < kHuffSlots * 256; i += kHuffThreads) {
+  for (int i = tid; i < kHuffSlots * (1 << kLutBits); i += (int)blockDim.x) (&T.lut[0][0])[i] = 0;
+  for (int i = tid; i < kHuffSlots * 256; i += (int)blockDim.x) {
     const int slot = i >> 8, k = i & 255, c = slot % 3;
     uint8_t v = 0;
     if (c < J.ncomp) v = slot < 3 ? (k < 16 ? J.dc_vals[J.comp_dc[c]][k] : 0) : J.ac_vals[J.comp_ac[c]][k];
@@ -672,11 +683,12 @@ __device__ __forceinline__ void build_tables(const ia_jpeg_job& J, HuffTables& T
 // predecessor's published record, repairs its first subsequences, publishes its own record and
 // only then writes coefficients.  Tickets are handed out in launch order, so the CTA a chunk
 // waits for is always already running.
-template <int kSub>
-__global__ void __launch_bounds__(kHuffThreads, 3) huffman_kernel(const ia_jpeg_job* __restrict__ jobs, int max_chunks,
-                                                               uint32_t* __restrict__ ticket_counter,
-                                                               int32_t* __restrict__ status) {
-  constexpr int kSubseqBits = kSub * 8;  // this instantiation's, not the namespace's
+template <int kThreads, int kMinBlocks, int kSub>
+__global__ void __launch_bounds__(kThreads, kMinBlocks) huffman_kernel(const ia_jpeg_job* __restrict__ jobs, int max_chunks,
+                                                                    uint32_t* __restrict__ ticket_counter,
+                                                                    int32_t* __restrict__ status) {
+  constexpr int kHuffThreads = kThreads;  // this instantiation's, not the namespace's
+  constexpr int kSubseqBits = kSub * 8;
   constexpr uint32_t kChunkBits = (uint32_t)kHuffThreads * kSubseqBits;
   __shared__ HuffTables T;
   // per subsequence: assumed entry state, resulting exit state and contribution
