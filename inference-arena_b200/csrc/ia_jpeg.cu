@@ -6,15 +6,18 @@
 // workspace carve and the launches.  Kernels: ia_jpeg_kernels.cuh —
 //   unstuff (count / scan / scatter): the entropy-coded bytes without FF00 stuffing and RSTn
 //       markers, plus where each restart segment begins and where the scan ends;
-//   huffman: one thread per 128-byte subsequence.  Huffman codes cannot be cut at arbitrary
+//   resync walk: for streams with damaged restart markers, libjpeg's resynchronisation as a
+//       table (which stretch of data belongs to which restart segment);
+//   huffman: one thread per 128- or 256-byte subsequence.  Huffman codes cannot be cut at arbitrary
 //       bits, so every thread first decodes from a guessed state (bit 0 of its subsequence,
 //       start of a block); a thread whose predecessor ended in a different state (bit
 //       position, block within the MCU, zig-zag index) decodes again from that state, until
 //       nothing changes — JPEG codes resynchronise within a few symbols, so this takes a
 //       handful of rounds instead of one serial walk (self-synchronising decode, Weissenberger
 //       & Schmidt 2018/2021).  A CTA scan of block counts and DC sums gives every thread its
-//       output block and DC predictors; one more pass writes the coefficients.  64 KB chunks
-//       of one image run in different CTAs, chained by a ticket-ordered look-back;
+//       output block and DC predictors; one more pass writes the coefficients (and conceals
+//       damaged segments the way jdhuff.c does).  The chunks of one image (32 to 128 KB) run in
+//       different CTAs, chained by a ticket-ordered look-back;
 //   idct: dequantise + libjpeg's jidctint.c "islow" integer IDCT, one thread per block;
 //   colour: libjpeg's fancy (triangle) chroma upsampling, jdcolor.c fixed-point YCbCr->RGB,
 //       EXIF orientation, RGB store.

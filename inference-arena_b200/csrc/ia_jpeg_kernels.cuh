@@ -4,11 +4,15 @@
 //                             survive (no FF00 stuffing, no RSTn markers), how many restart
 //                             markers, where the scan ends (first other marker)
 //   U2 unstuff_scan_kernel    per image: exclusive scan of the tile counts, totals
-//   U3 unstuff_scatter_kernel per tile: write the clean stream and the segment starts
-//   H  huffman_kernel         one CTA per 64 KB chunk of the clean stream (512 subsequences of
-//                             128 bytes, one per thread), self-synchronising decode inside
-//                             the CTA, chunks chained through a ticketed look-back
-//   I  idct_kernel            one thread per 8x8 block, jidctint.c "islow"
+//   U3 unstuff_scatter_kernel per tile: write the clean stream, the region starts and the code
+//                             of every marker inside the data
+//   R  resync_walk_kernel     damaged restart markers only: which region of the stream is which
+//                             restart segment, the way libjpeg's resynchronisation decides it
+//   H  huffman_kernel         one CTA per chunk of the clean stream (256 or 512 subsequences of
+//                             128 or 256 bytes, one per thread: 32 to 128 KB), self-synchronising
+//                             decode inside the CTA, chunks chained through a ticketed look-back,
+//                             libjpeg's concealment of damaged segments in the write pass
+//   I  idct_kernel            one thread per 8x8 block, jidctint.c "islow" as the SIMD code evaluates it
 //   C  colour_kernel          eight pixels per thread: fancy upsampling, YCbCr->RGB, orientation
 #pragma once
 
