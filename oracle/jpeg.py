@@ -8,9 +8,17 @@ dependency that is not under /root/reference: OpenCV's bundled libjpeg-turbo (op
 4.13.0 here bundles 3.1.2; the reference pins opencv-python 4.11.0.86).  This module restates
 libjpeg(-turbo)'s published decoder with its default settings, the ones OpenCV uses:
 
-  * sequential Huffman decoding, ITU T.81 Annex F.2.2 (jdhuff.c);
+  * the header checks that make libjpeg give up (jdmarker.c, jdinput.c, jdhuff.c table
+    validation) and the standard Huffman tables it installs when a file has none;
+  * sequential Huffman decoding, ITU T.81 Annex F.2.2 (jdhuff.c), including what it does with
+    damaged data: invalid codes, runs past the end of a block, zero bits behind a marker and
+    the MCUs left zero after them, restarts by MCU count and the marker resynchronisation of
+    jdmarker.c jpeg_resync_to_restart; data that ends without a marker raises, as OpenCV's
+    source manager makes libjpeg fail there;
   * dequantisation + the "slow-but-accurate" integer inverse DCT, jidctint.c
-    (CONST_BITS 13, PASS1_BITS 2, Loeffler-Ligtenberg-Moschytz), JDCT_ISLOW;
+    (CONST_BITS 13, PASS1_BITS 2, Loeffler-Ligtenberg-Moschytz), JDCT_ISLOW, evaluated the way
+    libjpeg-turbo's SIMD code does (16-bit lanes, saturating packs): identical to the C code
+    for every block an encoder produces, and what cv2 returns for garbage coefficients;
   * "fancy" (triangle-filter) chroma upsampling, jdsample.c: h2v1, h2v2, h1v2; plain
     replication when the subsampled width is <= 2 or for other integral factors;
   * YCbCr -> RGB with the 16-bit fixed-point tables of jdcolor.c; grayscale replicated;
@@ -18,8 +26,9 @@ libjpeg(-turbo)'s published decoder with its default settings, the ones OpenCV u
     loadsave.cpp ApplyExifOrientation).
 
 It is pinned by tests/test_oracle_jpeg.py against ``cv2.imdecode`` itself (every sampling
-mode, odd sizes, restart intervals, optimised tables, qualities 5..100) and against the
-committed fixtures produced through the reference's own ``load_image_from_bytes``
+mode, odd sizes, restart intervals, optimised tables, qualities 5..100; damaged headers through
+scripts/jpeg_header_fuzz.py; cut, renumbered and damaged scans) and against the committed
+fixtures produced through the reference's own ``load_image_from_bytes``
 (tests/golden/make_golden.py).  Pure-Python loops: meant for small images.
 """
 
