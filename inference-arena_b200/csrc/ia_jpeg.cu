@@ -445,8 +445,9 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
   }
   // Configuration of the Huffman kernel (measured cross-overs, see ia_jpeg_kernels.cuh):
   // 256 threads x 128-byte subsequences (32 KB chunks) for a few frames, 256-byte subsequences
-  // once the batch holds enough chunks, and 512 threads x 256 bytes (128 KB chunks) for large
-  // batches of large files.  IA_JPEG_SUBSEQ=128|256 and IA_JPEG_THREADS=256|512 override.
+  // once the batch holds enough chunks.  The 512-thread instantiations are kept for
+  // IA_JPEG_THREADS=512 (IA_JPEG_SUBSEQ=128|256 forces the other choice): they win by 4 % at
+  // exactly 64 x 1080p and lose at 32, at 128 and on 4K frames, so they are not chosen.
   unsigned long long total_bytes = 0, ctas_large_sub = 0;
   uint32_t max_scan = 0;
   for (int i = 0; i < n; ++i) {
@@ -459,9 +460,8 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
   static const int forced_threads = [] { const char* e = getenv("IA_JPEG_THREADS"); return e ? atoi(e) : 0; }();
   const unsigned long long avg_bytes = total_bytes / (unsigned)n;
   const bool large_files = avg_bytes >= kLargeFileBytes;
-  int threads = large_files && total_bytes >= kLargeBatchBytes ? kHuffThreadsLarge : kHuffThreads;
-  int sub = threads == kHuffThreadsLarge || ctas_large_sub >= kLargeSubseqCtasFrom ||
-                    (large_files && total_bytes >= kLargeSubseqBytesFrom)
+  int threads = kHuffThreads;
+  int sub = ctas_large_sub >= kLargeSubseqCtasFrom || (large_files && total_bytes >= kLargeSubseqBytesFrom)
                 ? kSubseqBytesLarge
                 : kSubseqBytes;
   if (forced_threads == kHuffThreads || forced_threads == kHuffThreadsLarge) threads = forced_threads;

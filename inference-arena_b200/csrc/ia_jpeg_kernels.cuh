@@ -30,17 +30,15 @@ constexpr int kSubseqBytesLarge = 256;
 // Cross-overs measured on B200 (profiles/README.md).  256-byte subsequences win once their CTAs
 // alone fill most of the GPU (256 x VGA: 1.93 -> 1.59 ms; 128 x VGA, 256 CTAs: 1.08 -> 1.26 ms),
 // and for large files — many chunks chained per image — already from a few megabytes (8 x 1080p
-// 1.03 -> 0.95 ms, one frame 0.54 -> 0.66 ms).  The 512-thread kernel wins only for big batches
-// of large files (64 x 1080p: 2.75 -> 2.63 ms; 32 x 1080p: 1.63 -> 1.83 ms).
+// 1.03 -> 0.95 ms, one frame 0.54 -> 0.66 ms).
 constexpr unsigned long long kLargeSubseqCtasFrom = 384;
 constexpr unsigned long long kLargeSubseqBytesFrom = 6ull << 20;
-constexpr unsigned long long kLargeBatchBytes = 40ull << 20;
 constexpr unsigned long long kLargeFileBytes = 256ull << 10;
 constexpr int kSubseqBits = kSubseqBytes * 8;
-// huffman_kernel comes as 256 threads x 4 CTAs per SM (64 registers, no spills: best latency and
-// best for small files) and as 512 threads x 3 CTAs (42 registers; with 256-byte subsequences its
-// 128 KB chunks are best for batches of large files).  The constants here are the smallest
-// configuration: they size the workspace.
+// huffman_kernel runs as 256 threads x 4 CTAs per SM (64 registers, nothing spilled).  512
+// threads x 3 CTAs (42 registers, the first shape of this kernel) is still instantiated for
+// comparison (IA_JPEG_THREADS=512): 4 % ahead at exactly 64 x 1080p, behind everywhere else
+// measured.  The constants here are the smallest configuration: they size the workspace.
 constexpr int kHuffThreads = 256;
 constexpr int kHuffThreadsLarge = 512;
 constexpr uint32_t kChunkBits = (uint32_t)kHuffThreads * kSubseqBits;
