@@ -325,7 +325,9 @@ size_t ia_jpeg_workspace_bytes(const ia_jpeg_job* jobs_host, int n);
 int ia_jpeg_plan(ia_jpeg_job* jobs_host, int n, const uint8_t* const* file_dev,
                  uint8_t* const* out_dev, void* workspace_dev, size_t workspace_bytes);
 /* jobs_dev: the planned job array copied to device memory by the caller (jobs_host is read
- * for launch geometry only).  status_dev int32 [n]: 0 = the pixels are libjpeg's;
+ * for launch geometry only).  status_dev int32 [n]: 0 = the pixels are libjpeg's (one known
+ * exception, damaged data only: an 8x8 block whose coefficients drive the 16-bit IDCT lanes
+ * to their limit);
  * bit 0 = a damaged stream (too few or too many blocks, restart markers out of place): it is
  * decoded and concealed the way libjpeg does it — cv2.imdecode warns "Corrupt JPEG data" and
  * returns these very pixels;

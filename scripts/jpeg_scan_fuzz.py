@@ -12,6 +12,7 @@ decodes, on how many of those the device returns the same pixels, and how the ve
 
 from __future__ import annotations
 
+import os
 import sys
 from pathlib import Path
 
@@ -30,7 +31,9 @@ from workloads import jpeg_cases as W  # noqa: E402
 def bases():
     out = []
     for i, (sampling, ri) in enumerate((("420", 0), ("420", 4), ("444", 1), ("422", 7), ("gray", 3), ("411", 0))):
-        img = W.photo(96, 152, seed=200 + i)
+        # IA_FUZZ_SIZE=HxW: larger frames put the damage into streams of several chained chunks
+        h, w = (int(v) for v in os.environ.get("IA_FUZZ_SIZE", "96x152").split("x"))
+        img = W.photo(h, w, seed=200 + i)
         data = W.encode(img[..., 0], 82, restart=ri) if sampling == "gray" else \
             W.encode(img, 82, sampling, restart=ri, optimize=bool(i & 1))
         out.append((data, M.parse_jpeg(data).scan_offset, ri))
