@@ -10,6 +10,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "../../include/ia_b200.h"
 
 namespace ia {
@@ -23,6 +27,28 @@ namespace ia {
 inline int launch_status() {
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? IA_OK : (int)e;
+}
+
+// Lift a kernel's dynamic shared-memory cap to the device's opt-in maximum, once per (kernel,
+// device).  The attribute belongs to the function and the device, not to a launch, and setting
+// it again with a smaller value LOWERS it: a launcher that set it to its own launch's size
+// could have it lowered by another host thread (another frame shape) between the call and the
+// launch.  So it is only ever set to the one largest value, under a lock.
+inline cudaError_t allow_max_dynamic_smem(const void* kernel) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, bool> done;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lock(mu);
+  bool& flag = done[std::make_pair(kernel, dev)];
+  if (flag) return cudaSuccess;
+  int optin = 0;
+  e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+  if (e == cudaSuccess) flag = true;
+  return e;
 }
 
 // ------------------------------------------------------------------- mbarrier / bulk copy

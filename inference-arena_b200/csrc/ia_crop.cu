@@ -248,7 +248,7 @@ extern "C" int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int sr
   int rc = launch_status();
   if (rc != IA_OK) return rc;
   return launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, nullptr, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
-                      out_size, mean, std, crops_dev, stream);
+                      out_size, mean, std, crops_dev, rois_dev + 6, stream);
 }
 
 extern "C" int ia_crop_resize_normalize_ragged(const ia_frame_desc* frames_dev, int n, int max_src_w,
@@ -282,7 +282,7 @@ extern "C" int ia_crop_resize_normalize_ragged(const ia_frame_desc* frames_dev, 
   int rc = launch_status();
   if (rc != IA_OK) return rc;
   return launch_crops(nullptr, 0, 1, max_src_w, frames_dev, rois_dev, roi_offsets_dev + n, 0, roi_capacity,
-                      out_size, mean, std, crops_dev, stream);
+                      out_size, mean, std, crops_dev, rois_dev + 6, stream);
 }
 
 extern "C" int ia_resize_normalize_rois(const uint8_t* frames_dev, int n, int src_h, int src_w,
@@ -293,7 +293,7 @@ extern "C" int ia_resize_normalize_rois(const uint8_t* frames_dev, int n, int sr
   if (num_rois == 0) return IA_OK;
   IA_RETURN_IF(!frames_dev || !rois_dev || !crops_dev || !mean || !std, IA_ERR_INVALID_ARGUMENT);
   return ia::launch_crops(frames_dev, (size_t)n * src_h * src_w * 3, src_h, src_w, nullptr, rois_dev, nullptr, num_rois, num_rois, out_size,
-                          mean, std, crops_dev, (cudaStream_t)stream);
+                          mean, std, crops_dev, nullptr, (cudaStream_t)stream);
 }
 
 extern "C" int ia_extract_crop_rects(const float* boxes_dev, int m, int cols, int image_index,

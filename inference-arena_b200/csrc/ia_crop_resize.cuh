@@ -1,26 +1,30 @@
 // ia_crop_resize.cuh — K4 stage B: ROI resize + normalise + CHW.
-// Warp-specialised, double-buffered, persistent.
+// Warp-specialised, double-buffered, persistent; separable like cv::resize itself.
 //
-// Work is a stream of steps; a step is up to 7 output rows (half of a 14-row band, fewer when
-// the crop rows are too wide for one staging buffer) of one ROI.  CTAs are persistent
-// (grid = SMs x resident CTAs) and stride over the (ROI, band) items; the ROI total is read
-// from device memory, so nothing returns to the host between NMS and here.  A CTA is
-// 7 consumer warps + 1 producer warp, coupled only by mbarriers (full / empty per staging
-// buffer) — no CTA-wide barrier in the loop:
+// One CTA per SM holds up to four independent TEAMS of 7 consumer warps + 1 producer warp and
+// one shared table of ((v/255 - mean)/std), replicated once per lane (bank) so that a warp's
+// 32 look-ups of 32 unrelated pixel values are one shared-memory wavefront.  A team strides
+// over work items of 28 output rows of one ROI (the ROI total is read from device memory:
+// nothing returns to the host between NMS and here) and walks an item in steps of up to 14
+// rows, coupled to its producer only by mbarriers (full / empty per staging buffer):
 //   producer: lane (row j, tap) evaluates OpenCV's yofs/beta entry, duplicates are removed
 //           with __match_any_sync and the copy geometry is worked out — all before waiting
 //           for the consumers to release the buffer; then the row plan is published and each
 //           distinct crop row segment is pulled into the staging buffer with one 1-D bulk
 //           async copy (TMA engine, complete_tx on full[buf]) of its 16-byte-aligned superset,
 //           clamped to the frame buffer (bytes a clamp cuts off are copied by the lane).
-//   consumers: one output row per warp, lanes over consecutive pixels.  The 6 source bytes of
-//           a pixel's two taps come from three aligned 32-bit shared loads + a funnel shift; a
-//           PRMT pairs (p[c], p[c+3]) and one IDP.2A does p0*a0 + p1*a1 against the packed
-//           coefficient pair — OpenCV's 11-bit fixed point, bit-identical to cv2.resize
-//           INTER_LINEAR (copy and the exact-2x box average use the same arithmetic with
-//           tables a0=b0=2048 resp. a0=a1=b0=b1=1024, which reduce to the identity and to
-//           (p00+p01+p10+p11+2)>>2).  Then the ((v/255 - mean)/std) LUT, replicated 4x across
-//           banks, and one 128-byte streaming store per warp and colour plane.
+//   consumers: a lane owns ONE output column for the whole item and walks down the rows; a
+//           warp is 32 neighbouring columns, so every plane store is one 128-byte line.  The
+//           lane's x coefficients live in registers (no table in shared memory).  The
+//           horizontal pass of a source row — three aligned 32-bit shared loads + a funnel
+//           shift for the 6 bytes of the two taps, a PRMT pairing (p[c], p[c+3]) and one
+//           IDP.2A against the packed coefficient pair, >> 4 — is evaluated once per source
+//           row and kept in registers for as long as output rows use it (two rows are live:
+//           an up-scaled crop reuses each ~2.5 times), which is the order cv::resize works in.
+//           The vertical step is two IMAD.HI against coefficients pre-shifted by 16 — OpenCV's
+//           11-bit fixed point, bit-identical to cv2.resize INTER_LINEAR (copy and the exact-2x
+//           box average use the same arithmetic with tables a0=b0=2048 resp.
+//           a0=a1=b0=b1=1024, which reduce to the identity and to (p00+p01+p10+p11+2)>>2).
 // The global side sees only wide, fully used requests; byte gathers hit shared memory.
 #pragma once
 
@@ -28,12 +32,14 @@
 
 namespace ia {
 
-// 7 consumer warps (one output row each per 7-row step; 224 = 7 x 32 pixels per row at
-// out_size 224, so no lane idles) + 1 producer warp = 256 threads.
-constexpr int kCropConsumers = 224;
-constexpr int kCropThreads = kCropConsumers + 32;
-constexpr int kBandRows = 14;  // two 7-row steps per band: one output row per consumer warp
-constexpr int kLutRep = 4;  // copies of each LUT entry, one per (lane & 3): fewer bank conflicts
+// 7 consumer warps (224 = 7 x 32 columns at out_size 224, so no lane idles) + 1 producer warp.
+constexpr int kTeamConsumers = 224;
+constexpr int kTeamThreads = kTeamConsumers + 32;
+constexpr int kMaxTeams = 4;
+constexpr int kItemRows = 28;  // output rows of one work item (8 items per 224-row ROI)
+constexpr int kStepRows = 14;  // rows per staging step: producer lane = (row, tap)
+constexpr int kLutRep = 32;    // one copy of the 3x256 table per bank
+constexpr int kLutFloats = 3 * 256 * kLutRep;
 
 struct CropParams {
   const uint8_t* frames;
@@ -45,20 +51,40 @@ struct CropParams {
   int total_host;        // used when total_dev is null
   int roi_slots;         // ROIs the output buffer can hold
   int out_size, bands;
-  int stage_bytes;  // bytes of ONE staging buffer (two follow each other in dynamic smem)
+  int teams;        // teams per CTA (blockDim.x = teams * kTeamThreads)
+  int stage_bytes;  // bytes of ONE staging buffer (each team has two)
+  // Work distribution.  With `tickets` (two zeroed ints: next item, teams finished) a team draws
+  // its items one at a time, so ROIs of very different cost still finish together; the last
+  // team to finish zeroes both again.  Without (the ROI table is read-only) teams stride.
+  int* tickets;
   float mean[3], stdv[3];
   float* out;
 };
 
-struct YPlan {
-  int off0, off1;  // byte offsets (within a staging buffer) of crop byte 0 of the two rows
-  int b0, b1;
+// One output row of a step.  A consumer lane keeps the horizontal passes of two source rows in
+// registers X and Y (a source row lives in the register of its parity, so the two taps of an
+// output row never collide); the producer, which knows the whole row sequence, tells it
+// which of them to refill — the shared-memory address of crop byte 0 of the staged row, or
+// -1 to keep what is there — and the vertical weight of each, shifted left by 16 for IMAD.HI
+// (0 for a tap that is not used).
+struct __align__(16) YPlan {
+  int src_x, src_y;
+  uint32_t w_x, w_y;
+};
+
+// Per-team control block in shared memory.
+struct __align__(16) TeamCtl {
+  YPlan plan[2][kStepRows];
+  double scx[2];  // OpenCV scale_x of the step's ROI, from the producer
+  int item[2];    // work item of the step in each buffer; -1 = no more work
+  int pad[2];
+  uint64_t full[2], empty[2];
 };
 
 // Position in the step stream; producer and consumers advance their own copy identically.
 struct Cursor {
   int item, sb, nsub, sub_rows;
-  int r, y_band, rows;  // ROI index, first output row of the band, rows in the band
+  int r, y_band, rows;  // ROI index, first output row of the item, rows in the item
   int empty, cw, ch, mode;
   int slot_bytes;
   const uint8_t* crop;     // first byte of the crop rectangle in the frame
@@ -66,14 +92,13 @@ struct Cursor {
   uintptr_t buf_lo, buf_hi;  // that frame's allocation: staging never reads outside it
 };
 
-__device__ __forceinline__ bool load_item(Cursor& c, const CropParams& p, int item, int items) {
+__device__ __forceinline__ void load_item(Cursor& c, const CropParams& p, int item) {
   c.item = item;
   c.sb = 0;
-  if (item >= items) return false;
   const int S = p.out_size;
   c.r = item / p.bands;
-  c.y_band = (item - c.r * p.bands) * kBandRows;
-  c.rows = min(kBandRows, S - c.y_band);
+  c.y_band = (item - c.r * p.bands) * kItemRows;
+  c.rows = min(kItemRows, S - c.y_band);
   const int* roi = p.rois + (size_t)c.r * 8;
   c.empty = roi[5];
   c.cw = c.empty ? 1 : roi[3] - roi[1];
@@ -93,30 +118,30 @@ __device__ __forceinline__ bool load_item(Cursor& c, const CropParams& p, int it
   }
   c.slot_bytes = (c.cw * 3 + 30 + 15) & ~15;  // aligned superset of one crop row segment
   const int max_slots = p.stage_bytes / c.slot_bytes;
-  const int cap = max(1, min(kBandRows, max_slots >> 1));  // two source rows per output row
+  const int cap = max(1, min(kStepRows, max_slots >> 1));  // two source rows per output row
   c.nsub = (c.rows + cap - 1) / cap;
   c.sub_rows = (c.rows + c.nsub - 1) / c.nsub;  // balanced split
-  return true;
-}
-
-__device__ __forceinline__ bool advance(Cursor& c, const CropParams& p, int items) {
-  if (++c.sb < c.nsub) return true;
-  return load_item(c, p, c.item + (int)gridDim.x, items);
 }
 
 // Producer warp: plan + stage the crop rows of step `c`; arrives on `full`.
 // Everything that does not touch shared memory (coefficients, duplicate removal, copy
-// geometry) is computed BEFORE waiting for the consumers to release the buffer.
+// geometry, which register each source row goes to) is computed BEFORE waiting for the
+// consumers to release the buffer.  held_x / held_y: the crop rows the consumers' registers hold
+// on entry (uniform across the warp), updated to what they hold after the step.
 __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& p, double sc_y,
-                                             uint8_t* stage, YPlan* plan, uint64_t* full,
-                                             uint64_t* empty, int empty_parity, double* scx_slot,
-                                             double sc_x, bool new_roi, int lane) {
+                                             uint8_t* stage, TeamCtl& ctl, int buf, int empty_parity,
+                                             double sc_x, bool new_roi, int& held_x, int& held_y, int lane) {
+  uint64_t* full = &ctl.full[buf];
+  uint64_t* empty = &ctl.empty[buf];
   if (c.empty) {  // nothing to stage; keep the barrier protocol uniform
     if (empty_parity >= 0) mbar_wait(empty, (uint32_t)empty_parity);
-    if (lane == 0) mbar_expect_tx(full, 0);
+    if (lane == 0) {
+      ctl.item[buf] = c.item;
+      mbar_expect_tx(full, 0);
+    }
     return;
   }
-  const int S = p.out_size;
+  YPlan* plan = ctl.plan[buf];
   const size_t row_bytes = c.row_bytes;
   const uintptr_t buf_lo = c.buf_lo, buf_hi = c.buf_hi;
   const int y0 = c.y_band + c.sb * c.sub_rows;
@@ -138,9 +163,33 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
       row = tap ? (k.w1 != 0 ? clampi(k.s0 + 1, 0, c.ch - 1) : -1) : clampi(k.s0, 0, c.ch - 1);
     }
   }
+  // ---- which register: a row goes to the register of its parity; a second tap clamped onto the
+  // first tap's row (bottom border) and an unused tap take the other one
+  const int row_first = __shfl_sync(0xffffffffu, row, lane & ~1);  // tap 0's row of this output row
+  const bool valid = row >= 0;
+  const int reg = tap == 0 ? (row & 1) : ((valid && row != row_first) ? (row & 1) : ((row_first & 1) ^ 1));
+  // what the register held before this output row: the closest earlier valid lane with the same
+  // register, else what it held on entry
+  const unsigned same_reg = __ballot_sync(0xffffffffu, reg == 1);
+  const unsigned valid_mask = __ballot_sync(0xffffffffu, valid);
+  const unsigned mine = (reg ? same_reg : ~same_reg) & valid_mask;
+  const unsigned before = mine & ((1u << lane) - 1u);
+  const int prev_lane = 31 - __clz(before);  // -1 when none
+  const int prev_row_l = __shfl_sync(0xffffffffu, row, prev_lane & 31);
+  const int prev_row = before ? prev_row_l : (reg ? held_y : held_x);
+  const bool refill = valid && row != prev_row;
+  {  // registers after the step
+    const unsigned mx = ~same_reg & valid_mask, my = same_reg & valid_mask;
+    const int lx = __shfl_sync(0xffffffffu, row, (31 - __clz(mx)) & 31);
+    const int ly = __shfl_sync(0xffffffffu, row, (31 - __clz(my)) & 31);
+    if (mx) held_x = lx;
+    if (my) held_y = ly;
+  }
+  // ---- staging: one slot per distinct row that some lane refills from
   const unsigned same = __match_any_sync(0xffffffffu, row);
+  const unsigned refills = __ballot_sync(0xffffffffu, refill);
   const int leader = __ffs(same) - 1;
-  const bool copy = leader == lane && row >= 0;
+  const bool copy = leader == lane && valid && (same & refills) != 0;
   const unsigned leaders = __ballot_sync(0xffffffffu, copy);
   const int slot = __popc(leaders & ((1u << leader) - 1u));
   const uintptr_t g_lo = (uintptr_t)(c.crop + (size_t)max(row, 0) * row_bytes);
@@ -158,7 +207,10 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
   for (int o = 16; o > 0; o >>= 1) tx += __shfl_xor_sync(0xffffffffu, tx, o);
 
   if (empty_parity >= 0) mbar_wait(empty, (uint32_t)empty_parity);  // consumers released the buffer
-  if (new_roi && lane == 0) *scx_slot = sc_x;  // OpenCV scale_x for the consumers' x table
+  if (lane == 0) {
+    ctl.item[buf] = c.item;
+    if (new_roi) ctl.scx[buf] = sc_x;  // OpenCV scale_x for the consumers' x coefficients
+  }
   if (copy) {
     if (bulk) {
       for (uintptr_t q = g_lo; q < a_lo; ++q) s[q - g_lo] = *reinterpret_cast<const uint8_t*>(q);
@@ -168,12 +220,14 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
     }
   }
   if (j < nr) {
-    if (tap == 0) {
-      plan[j].off0 = off;
-      plan[j].b0 = b0;
-      plan[j].b1 = b1;
+    const int src = refill ? (int)smem_u32(s) : -1;
+    const uint32_t w = valid ? (uint32_t)(tap ? b1 : b0) << 16 : 0u;
+    if (reg == 0) {
+      plan[j].src_x = src;
+      plan[j].w_x = w;
     } else {
-      plan[j].off1 = row >= 0 ? off : 0;  // unused tap: any valid offset, its weight is 0
+      plan[j].src_y = src;
+      plan[j].w_y = w;
     }
   }
   __syncwarp();  // plan and lane-copied bytes are ordered before the releasing arrive
@@ -182,144 +236,197 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
   if (bulk) bulk_g2s(s + (ptrdiff_t)(a_lo - g_lo), reinterpret_cast<const void*>(a_lo), bulk, full);
 }
 
-__global__ void __launch_bounds__(kCropThreads, 4) crop_resize_kernel(const CropParams p) {
+// Horizontal pass of one staged source row at this lane's column: (p[x0]*a0 + p[x1]*a1) >> 4 per
+// channel (HResizeLinear + the >> 4 VResizeLinear applies to its int32 rows).  `a` is the
+// shared-memory address of the first tap's R byte.
+__device__ __forceinline__ void hpass(uint32_t a, uint32_t coef, uint32_t& h0, uint32_t& h1, uint32_t& h2) {
+  const uint32_t w = a & ~3u;
+  uint32_t w0, w1, w2;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(w));
+  asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(w1) : "r"(w));
+  asm volatile("ld.shared.u32 %0, [%1+8];" : "=r"(w2) : "r"(w));
+  const uint32_t sh = a << 3;  // the funnel shift takes it modulo 32: (a & 3) * 8
+  const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+  // a zero weight multiplies whatever byte sits there (always inside the staging buffer) by 0
+  h0 = __dp2a_lo(coef, tap_pair(lo, hi, 0), 0u) >> 4;
+  h1 = __dp2a_lo(coef, tap_pair(lo, hi, 1), 0u) >> 4;
+  h2 = __dp2a_lo(coef, tap_pair(lo, hi, 2), 0u) >> 4;
+}
+
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
+// kFixed224: out_size == 224 (MobileNet's): one column per consumer lane, every stride a constant.
+template <bool kFixed224>
+__global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kernel(const CropParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ float lut[3][256 * kLutRep];
-  __shared__ YPlan yplan[2][kBandRows];
-  __shared__ double scx[2];  // OpenCV scale_x of the step's ROI, from the producer
-  __shared__ __align__(8) uint64_t full[2], empty[2];
+  float* lut = reinterpret_cast<float*>(smem);  // [3][256][32]
+  uint8_t* stage_all = smem + kLutFloats * sizeof(float);
+  TeamCtl* ctl_all = reinterpret_cast<TeamCtl*>(stage_all + (size_t)p.teams * 2 * p.stage_bytes);
 
   const int tid = threadIdx.x, lane = tid & 31;
-  const int S = p.out_size;
-  const int xg = (S + 3) >> 2;
-  int* xoff = reinterpret_cast<int*>(smem + 2 * (size_t)p.stage_bytes);  // [2][4*xg] int2 (offset, coefs)
+  const int team = tid / kTeamThreads, ttid = tid - team * kTeamThreads;
+  const int S = kFixed224 ? 224 : p.out_size;
   const int total = p.total_dev ? min(*p.total_dev, p.roi_slots) : p.total_host;
   const int items = total * p.bands;
+  if (items <= 0) return;  // (the ticket words are only valid when ROI 0 exists)
   const size_t plane = (size_t)S * S;
+  TeamCtl& ctl = ctl_all[team];
+  uint8_t* stage = stage_all + (size_t)team * 2 * p.stage_bytes;
 
-  for (int i = tid; i < 256 * kLutRep; i += kCropThreads) {
-    const float u = __fdiv_rn((float)(i / kLutRep), 255.0f);  // transforms.py:263
+  // the table: 768 values, each written as one 128-byte row (a copy per bank)
+  for (int i = tid; i < 3 * 256; i += blockDim.x) {
+    const int c = i >> 8;
+    const float u = __fdiv_rn((float)(i & 255), 255.0f);                    // transforms.py:263
+    const float mean = c == 0 ? p.mean[0] : (c == 1 ? p.mean[1] : p.mean[2]);
+    const float stdv = c == 0 ? p.stdv[0] : (c == 1 ? p.stdv[1] : p.stdv[2]);
+    const float f = __fdiv_rn(__fsub_rn(u, mean), stdv);                     // :270
+    float4* row = reinterpret_cast<float4*>(lut + (size_t)i * kLutRep);
 #pragma unroll
-    for (int c = 0; c < 3; ++c) lut[c][i] = __fdiv_rn(__fsub_rn(u, p.mean[c]), p.stdv[c]);  // :270
+    for (int k = 0; k < kLutRep / 4; ++k) row[k] = make_float4(f, f, f, f);
   }
-  if (tid == 0) {
-    mbar_init(&full[0], 1);
-    mbar_init(&full[1], 1);
-    mbar_init(&empty[0], kCropConsumers / 32);
-    mbar_init(&empty[1], kCropConsumers / 32);
+  if (ttid == 0) {
+    mbar_init(&ctl.full[0], 1);
+    mbar_init(&ctl.full[1], 1);
+    mbar_init(&ctl.empty[0], kTeamConsumers / 32);
+    mbar_init(&ctl.empty[1], kTeamConsumers / 32);
     mbar_fence_init();
   }
   __syncthreads();
 
-  Cursor cur;
-  bool have = load_item(cur, p, blockIdx.x, items);
-
-  if (tid >= kCropConsumers) {
+  if (ttid >= kTeamConsumers) {
     // =============================== producer warp ====================================
-    double sc_y = 0.0;
-    for (int s = 0; have; ++s) {
-      const int buf = s & 1;
-      const int empty_parity = s >= 2 ? (((s >> 1) - 1) & 1) : -1;
-      double sc_x = 0.0;
-      const bool new_roi = cur.sb == 0 && !cur.empty;
-      if (new_roi) {
-        sc_y = axis_scale(S, cur.ch);
-        sc_x = axis_scale(S, cur.cw);
+    const int n_teams = (int)gridDim.x * p.teams;
+    auto next_item = [&](int current) -> int {
+      int it;
+      if (p.tickets != nullptr) {
+        it = lane == 0 ? atomicAdd(p.tickets, 1) : 0;
+        it = __shfl_sync(0xffffffffu, it, 0);
+      } else {
+        it = current < 0 ? (int)blockIdx.x * p.teams + team : current + n_teams;
       }
-      produce_step(cur, p, sc_y, smem + (size_t)buf * p.stage_bytes, yplan[buf], &full[buf], &empty[buf],
-                   empty_parity, &scx[buf], sc_x, new_roi, lane);
-      have = advance(cur, p, items);
+      return it < items ? it : -1;
+    };
+    Cursor cur;
+    double sc_y = 0.0;
+    int held_x = -2, held_y = -2;
+    int s = 0;
+    for (int item = next_item(-1); item >= 0; item = next_item(item)) {
+      load_item(cur, p, item);
+      held_x = held_y = -2;  // a new item starts with nothing in the consumers' registers
+      for (; cur.sb < cur.nsub; ++cur.sb, ++s) {
+        // more than 224 columns: a lane walks the step once per column chunk, so nothing carries over
+        if (!kFixed224 && S > kTeamConsumers) held_x = held_y = -2;
+        const int buf = s & 1;
+        const int empty_parity = s >= 2 ? (((s >> 1) - 1) & 1) : -1;
+        double sc_x = 0.0;
+        const bool new_roi = cur.sb == 0 && !cur.empty;
+        if (new_roi) {
+          sc_y = axis_scale(S, cur.ch);
+          sc_x = axis_scale(S, cur.cw);
+        }
+        produce_step(cur, p, sc_y, stage + (size_t)buf * p.stage_bytes, ctl, buf, empty_parity, sc_x, new_roi,
+                     held_x, held_y, lane);
+      }
+    }
+    {  // the end marker travels like a step
+      const int buf = s & 1;
+      if (s >= 2) mbar_wait(&ctl.empty[buf], (uint32_t)(((s >> 1) - 1) & 1));
+      if (lane == 0) {
+        ctl.item[buf] = -1;
+        mbar_expect_tx(&ctl.full[buf], 0);
+        if (p.tickets != nullptr && atomicAdd(p.tickets + 1, 1) == n_teams - 1) {
+          p.tickets[0] = 0;  // every team has drawn its last ticket: leave the words as they were
+          p.tickets[1] = 0;
+        }
+      }
     }
     return;
   }
 
   // ================================= consumer warps ====================================
-  const int rep = lane & (kLutRep - 1);
-  int n_item = 0;
-  for (int s = 0; have; ++s) {
+  const uint32_t lut_lane = smem_u32(lut) + ((uint32_t)lane << 2);
+  const int col0 = ttid;  // this lane's column within a 224-column chunk
+  uint32_t hx0 = 0, hx1 = 0, hx2 = 0, hy0 = 0, hy1 = 0, hy2 = 0;  // the two live horizontal passes
+  int xo = 0;
+  uint32_t coef = 0;
+  double sc_x = 0.0;  // of the current item's ROI
+  Cursor cur;
+  cur.item = -1;
+  for (int s = 0;; ++s) {
     const int buf = s & 1;
-    mbar_wait(&full[buf], (s >> 1) & 1);
-    if (cur.sb == 0) {
-      if (!cur.empty) {
-        // x table of this ROI, double-buffered by the parity of the NON-EMPTY items (an empty
-        // ROI has no table and no barrier, so it must not flip the parity), then a
-        // consumers-only barrier: a warp can only overwrite a table two barriers after the
-        // slowest warp last read it
-        ++n_item;
-        int2* xt_w = reinterpret_cast<int2*>(xoff + (n_item & 1) * 8 * xg);
-        const double sc_x = scx[buf];
-        for (int x = tid; x < S; x += kCropConsumers) {
-          int xo, a0, a1;
-          if (cur.mode == kResizeCopy) {
-            xo = x * 3, a0 = kCoefOne, a1 = 0;
-          } else if (cur.mode == kResizeBox2) {
-            xo = x * 6, a0 = a1 = kCoefOne / 2;
-          } else {
-            const AxisCoef k = axis_coef(x, sc_x, cur.cw, true);
-            xo = k.s0 * 3, a0 = k.w0, a1 = k.w1;
-          }
-          xt_w[x] = make_int2(xo, a0 | (a1 << 16));
-        }
-        named_barrier_sync(1, kCropConsumers);
-      }
-    }
-
-    const uint32_t* stage32 = reinterpret_cast<const uint32_t*>(smem + (size_t)buf * p.stage_bytes);
-    const int2* xt = reinterpret_cast<const int2*>(xoff + (n_item & 1) * 8 * xg);  // (byte offset, a0 | a1 << 16)
+    mbar_wait(&ctl.full[buf], (s >> 1) & 1);
+    const int item = ctl.item[buf];
+    if (item < 0) break;
+    if (item != cur.item) load_item(cur, p, item);
     const int y0 = cur.y_band + cur.sb * cur.sub_rows;
     const int nr = min(cur.sub_rows, cur.rows - cur.sb * cur.sub_rows);
-    const int warp = tid >> 5;
+    float* const obase = p.out + ((size_t)cur.r * 3) * plane + (size_t)y0 * S;
+    if (cur.sb == 0 && !cur.empty) sc_x = ctl.scx[buf];
 
-    // one output row per warp, lanes over consecutive pixels: neighbouring lanes read
-    // neighbouring (often the same) staging words and write one 128-byte line per plane
-    for (int j = warp; j < nr; j += kCropConsumers / 32) {
-      float* orow = p.out + ((size_t)cur.r * 3) * plane + (size_t)(y0 + j) * S;
-      if (cur.empty) {
-        for (int x = lane; x < S; x += 32) {  // mobilenet_preprocess.py:266-267: a 1x1 black crop
-#pragma unroll
-          for (int c = 0; c < 3; ++c) st_stream_f1(orow + c * plane + x, lut[c][rep]);
+    if (cur.empty) {
+      // mobilenet_preprocess.py:266-267: a 1x1 black crop
+      const float e0 = lds_f32(lut_lane), e1 = lds_f32(lut_lane + 256 * kLutRep * 4),
+                  e2 = lds_f32(lut_lane + 512 * kLutRep * 4);
+      for (int x = col0; x < S; x += kTeamConsumers) {
+        float* o = obase + x;
+        for (int j = 0; j < nr; ++j, o += S) {
+          st_stream_f1(o, e0);
+          st_stream_f1(o + plane, e1);
+          st_stream_f1(o + 2 * plane, e2);
         }
-        continue;
       }
-      const YPlan yp = yplan[buf][j];
-      // one pointer per colour plane, advanced by a constant: under the unroll the stores use
-      // immediate offsets instead of 64-bit address arithmetic per element
-      float* o0 = orow + lane;
-      float* o1 = o0 + plane;
-      float* o2 = o1 + plane;
-      auto pixel = [&](const int2 e, float* d0, float* d1, float* d2) {
-        uint32_t lo0, hi0, lo1, hi1;
-        load6(stage32, yp.off0 + e.x, lo0, hi0);
-        load6(stage32, yp.off1 + e.x, lo1, hi1);
-        float* const dst[3] = {d0, d1, d2};
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          // h = p[c]*a0 + p[c+3]*a1 in one IDP.2A; a zero weight multiplies whatever byte sits
-          // there (always inside the staging buffer) by 0
-          const int h0 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo0, hi0, c), 0u);
-          const int h1 = (int)__dp2a_lo((uint32_t)e.y, tap_pair(lo1, hi1, c), 0u);
-          const int v = vresize(h0, h1, yp.b0, yp.b1);
-          st_stream_f1(dst[c], lut[c][v * kLutRep + rep]);
+    } else {
+      const int chunks = kFixed224 ? 1 : (S + kTeamConsumers - 1) / kTeamConsumers;
+      for (int xb = 0; xb < chunks; ++xb) {
+        const int x = xb * kTeamConsumers + col0;
+        const bool live = kFixed224 || x < S;
+        if (cur.sb == 0 || chunks > 1) {
+          // this lane's x coefficients (xofs / alpha entry), kept in registers for the whole item
+          xo = 0, coef = 0;
+          if (live) {
+            if (cur.mode == kResizeCopy) {
+              xo = x * 3, coef = kCoefOne;
+            } else if (cur.mode == kResizeBox2) {
+              xo = x * 6, coef = (kCoefOne / 2) | ((kCoefOne / 2) << 16);
+            } else {
+              const AxisCoef k = axis_coef(x, sc_x, cur.cw, true);
+              xo = k.s0 * 3, coef = (uint32_t)k.w0 | ((uint32_t)k.w1 << 16);
+            }
+          }
         }
-      };
-      if (S == 7 * 32) {  // MobileNet's 224: a fixed trip count, so every offset is an immediate
-        const int2* xl = xt + lane;
-#pragma unroll
-        for (int k = 0; k < 7; ++k) pixel(xl[32 * k], o0 + 32 * k, o1 + 32 * k, o2 + 32 * k);
-      } else {
-#pragma unroll 4
-        for (int x = lane; x < S; x += 32, o0 += 32, o1 += 32, o2 += 32) pixel(xt[x], o0, o1, o2);
+        float* o = obase + x;
+        const YPlan* plan = ctl.plan[buf];
+        for (int j = 0; j < nr; ++j, o += S) {
+          const int4 pl = *reinterpret_cast<const int4*>(&plan[j]);  // src_x src_y w_x w_y, warp-uniform
+          if (pl.x >= 0) hpass((uint32_t)(pl.x + xo), coef, hx0, hx1, hx2);
+          if (pl.y >= 0) hpass((uint32_t)(pl.y + xo), coef, hy0, hy1, hy2);
+          // VResizeLinear: (((b0*(h0>>4))>>16) + ((b1*(h1>>4))>>16) + 2) >> 2; an unused tap has
+          // weight 0 and multiplies whatever its register holds by 0
+          const uint32_t t0 = __umulhi((uint32_t)pl.z, hx0) + __umulhi((uint32_t)pl.w, hy0) + 2u;
+          const uint32_t t1 = __umulhi((uint32_t)pl.z, hx1) + __umulhi((uint32_t)pl.w, hy1) + 2u;
+          const uint32_t t2 = __umulhi((uint32_t)pl.z, hx2) + __umulhi((uint32_t)pl.w, hy2) + 2u;
+          if (live) {
+            // table row (t >> 2) is 128 bytes; this lane's copy sits at lane * 4 inside it
+            st_stream_f1(o, lds_f32(lut_lane + ((t0 & ~3u) << 5)));
+            st_stream_f1(o + plane, lds_f32(lut_lane + 256 * kLutRep * 4 + ((t1 & ~3u) << 5)));
+            st_stream_f1(o + 2 * plane, lds_f32(lut_lane + 512 * kLutRep * 4 + ((t2 & ~3u) << 5)));
+          }
+        }
       }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[buf]);  // this warp is done with the staging buffer + plan
-    have = advance(cur, p, items);
+    if (lane == 0) mbar_arrive(&ctl.empty[buf]);  // this warp is done with the staging buffer + plan
+    ++cur.sb;
   }
 }
 
 static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, int src_w,
                         const ia_frame_desc* descs, const int* rois, const int* total_dev, int total_host, int roi_slots,
-                        int out_size, const float mean[3], const float stdv[3], float* out,
+                        int out_size, const float mean[3], const float stdv[3], float* out, int* tickets,
                         cudaStream_t stream) {
   if (roi_slots == 0) return IA_OK;
   CropParams c;
@@ -333,34 +440,40 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   c.total_host = total_host;
   c.roi_slots = roi_slots;
   c.out_size = out_size;
-  c.bands = (out_size + kBandRows - 1) / kBandRows;
+  c.bands = (out_size + kItemRows - 1) / kItemRows;
   for (int i = 0; i < 3; ++i) {
     c.mean[i] = mean[i];
     c.stdv[i] = stdv[i];
   }
   c.out = out;
+  c.tickets = tickets;
   const long long items = (long long)c.bands * roi_slots;
   IA_RETURN_IF(items > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
-  // two staging buffers; each holds at least two full-width rows, normally 19 KB
-  const size_t widest = ((size_t)src_w * 3 + 30 + 15) & ~(size_t)15;
-  size_t stage = 19 * 1024;  // with the 4x LUT and 64 registers: 4 CTAs (28 consumer warps) per SM
-  if (stage < 2 * widest) stage = 2 * widest;
-  const size_t xg = ((size_t)out_size + 3) / 4;
-  const size_t smem = 2 * stage + 4 * xg * sizeof(int4);
-  IA_RETURN_IF(smem > 180 * 1024 || stage >= (1u << 20), IA_ERR_UNSUPPORTED);
-  c.stage_bytes = (int)stage;
-  int dev = 0, sms = 148, per_sm = 1;
+  int dev = 0, sms = 148, optin = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(crop_resize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e == cudaSuccess)
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, crop_resize_kernel, kCropThreads, smem);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   if (e != cudaSuccess) return (int)e;
-  if (per_sm < 1) per_sm = 1;
-  const long long resident = (long long)sms * per_sm;
-  const long long grid = items < resident ? items : resident;
-  crop_resize_kernel<<<(unsigned)grid, kCropThreads, smem, stream>>>(c);
+  // shared memory of the one CTA per SM: the table, then per team two staging buffers (each at
+  // least two full-width rows) and a control block.  Narrow frames get four teams of ~16 KB
+  // buffers; wide ones fewer teams with larger buffers.
+  const size_t widest = ((size_t)src_w * 3 + 30 + 15) & ~(size_t)15;
+  const size_t fixed = kLutFloats * sizeof(float) + kMaxTeams * sizeof(TeamCtl);
+  IA_RETURN_IF((size_t)optin < fixed + 4 * widest, IA_ERR_UNSUPPORTED);
+  const size_t avail = (size_t)optin - fixed;
+  int teams = (int)(avail / (4 * widest));
+  if (teams > kMaxTeams) teams = kMaxTeams;
+  const size_t stage = (avail / ((size_t)teams * 2)) & ~(size_t)127;
+  IA_RETURN_IF(stage >= (1u << 20), IA_ERR_UNSUPPORTED);
+  c.teams = teams;
+  c.stage_bytes = (int)stage;
+  const size_t smem = kLutFloats * sizeof(float) + (size_t)teams * 2 * stage + (size_t)teams * sizeof(TeamCtl);
+  void (*kernel)(CropParams) = out_size == 224 ? crop_resize_kernel<true> : crop_resize_kernel<false>;
+  e = allow_max_dynamic_smem(reinterpret_cast<const void*>(kernel));
+  if (e != cudaSuccess) return (int)e;
+  const long long want = (items + teams - 1) / teams;
+  const long long grid = want < sms ? want : sms;
+  kernel<<<(unsigned)grid, teams * kTeamThreads, smem, stream>>>(c);
   return launch_status();
 }
 
