@@ -38,6 +38,7 @@ constexpr int kTeamThreads = kTeamConsumers + 32;
 constexpr int kMaxTeams = 4;
 constexpr int kItemRows = 28;  // output rows of one work item (8 items per 224-row ROI)
 constexpr int kStepRows = 14;  // rows per staging step: producer lane = (row, tap)
+constexpr int kStages = 2;     // staging buffers per team
 constexpr int kLutRep = 32;    // one copy of the 3x256 table per bank
 constexpr int kLutFloats = 3 * 256 * kLutRep;
 
@@ -52,7 +53,7 @@ struct CropParams {
   int roi_slots;         // ROIs the output buffer can hold
   int out_size, bands;
   int teams;        // teams per CTA (blockDim.x = teams * kTeamThreads)
-  int stage_bytes;  // bytes of ONE staging buffer (each team has two)
+  int stage_bytes;  // bytes of ONE staging buffer (each team has kStages)
   // Work distribution.  With `tickets` (two zeroed ints: next item, teams finished) a team draws
   // its items one at a time, so ROIs of very different cost still finish together; the last
   // team to finish zeroes both again.  Without (the ROI table is read-only) teams stride.
@@ -72,16 +73,49 @@ struct __align__(16) YPlan {
   uint32_t w_x, w_y;
 };
 
-// Per-team control block in shared memory.
-struct __align__(16) TeamCtl {
-  YPlan plan[2][kStepRows];
-  double scx[2];  // OpenCV scale_x of the step's ROI, from the producer
-  int item[2];    // work item of the step in each buffer; -1 = no more work
-  int pad[2];
-  uint64_t full[2], empty[2];
+enum : int { kStepFirst = 1, kStepEmpty = 2, kStepModeShift = 2 };
+
+// What the consumers need to know about a step; they never read the ROI table themselves.
+struct __align__(16) StepInfo {
+  int item;    // -1: no more work
+  int roi;     // ROI slot in the output
+  int y0, nr;  // first output row and number of rows of the step
+  int flags;   // kStepFirst: first step of an item; kStepEmpty: empty ROI; mode << kStepModeShift
+  int cw;      // crop width
+  double scx;  // OpenCV scale_x of the ROI
 };
 
-// Position in the step stream; producer and consumers advance their own copy identically.
+// Per-team control block in shared memory.
+struct __align__(16) TeamCtl {
+  YPlan plan[kStages][kStepRows];
+  StepInfo info[kStages];
+  uint64_t full[kStages], empty[kStages];
+};
+
+// The ROI record of a work item (and its frame, for ragged batches), read ahead of its use.
+struct ItemRecord {
+  int item;
+  int4 a, b;  // image x1 y1 x2 | y2 empty - -
+  ia_frame_desc d;
+};
+
+__device__ __forceinline__ ItemRecord fetch_item(const CropParams& p, int item) {
+  ItemRecord r;
+  r.item = item;
+  r.a = make_int4(0, 0, 0, 0);
+  r.b = make_int4(0, 1, 0, 0);
+  r.d.data_dev = nullptr;
+  r.d.h = r.d.w = 0;
+  if (item >= 0) {
+    const int4* roi = reinterpret_cast<const int4*>(p.rois + (size_t)(item / p.bands) * 8);
+    r.a = roi[0];
+    r.b = roi[1];
+    if (p.descs != nullptr) r.d = p.descs[r.a.x];
+  }
+  return r;
+}
+
+// A work item as the producer sees it.
 struct Cursor {
   int item, sb, nsub, sub_rows;
   int r, y_band, rows;  // ROI index, first output row of the item, rows in the item
@@ -92,29 +126,27 @@ struct Cursor {
   uintptr_t buf_lo, buf_hi;  // that frame's allocation: staging never reads outside it
 };
 
-__device__ __forceinline__ void load_item(Cursor& c, const CropParams& p, int item) {
-  c.item = item;
+__device__ __forceinline__ void load_item(Cursor& c, const CropParams& p, const ItemRecord& rec) {
+  c.item = rec.item;
   c.sb = 0;
   const int S = p.out_size;
-  c.r = item / p.bands;
-  c.y_band = (item - c.r * p.bands) * kItemRows;
+  c.r = rec.item / p.bands;
+  c.y_band = (rec.item - c.r * p.bands) * kItemRows;
   c.rows = min(kItemRows, S - c.y_band);
-  const int* roi = p.rois + (size_t)c.r * 8;
-  c.empty = roi[5];
-  c.cw = c.empty ? 1 : roi[3] - roi[1];
-  c.ch = c.empty ? 1 : roi[4] - roi[2];
+  c.empty = rec.b.y;
+  c.cw = c.empty ? 1 : rec.a.w - rec.a.y;
+  c.ch = c.empty ? 1 : rec.b.x - rec.a.z;
   c.mode = resize_mode(c.ch, c.cw, S, S);
   if (p.descs != nullptr) {
-    const ia_frame_desc d = p.descs[roi[0]];
-    c.row_bytes = (uint32_t)d.w * 3u;
-    c.buf_lo = (uintptr_t)d.data_dev;
-    c.buf_hi = c.buf_lo + (size_t)d.h * c.row_bytes;
-    c.crop = d.data_dev + (size_t)roi[2] * c.row_bytes + (size_t)roi[1] * 3;
+    c.row_bytes = (uint32_t)rec.d.w * 3u;
+    c.buf_lo = (uintptr_t)rec.d.data_dev;
+    c.buf_hi = c.buf_lo + (size_t)rec.d.h * c.row_bytes;
+    c.crop = rec.d.data_dev + (size_t)rec.a.z * c.row_bytes + (size_t)rec.a.y * 3;
   } else {
     c.row_bytes = (uint32_t)p.src_w * 3u;
     c.buf_lo = (uintptr_t)p.frames;
     c.buf_hi = c.buf_lo + p.frames_bytes;
-    c.crop = p.frames + ((size_t)roi[0] * p.src_h + roi[2]) * c.row_bytes + (size_t)roi[1] * 3;
+    c.crop = p.frames + ((size_t)rec.a.x * p.src_h + rec.a.z) * c.row_bytes + (size_t)rec.a.y * 3;
   }
   c.slot_bytes = (c.cw * 3 + 30 + 15) & ~15;  // aligned superset of one crop row segment
   const int max_slots = p.stage_bytes / c.slot_bytes;
@@ -128,15 +160,25 @@ __device__ __forceinline__ void load_item(Cursor& c, const CropParams& p, int it
 // geometry, which register each source row goes to) is computed BEFORE waiting for the
 // consumers to release the buffer.  held_x / held_y: the crop rows the consumers' registers hold
 // on entry (uniform across the warp), updated to what they hold after the step.
-__device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& p, double sc_y,
-                                             uint8_t* stage, TeamCtl& ctl, int buf, int empty_parity,
-                                             double sc_x, bool new_roi, int& held_x, int& held_y, int lane) {
+__device__ __forceinline__ void produce_step(const Cursor& c, double sc_y, double sc_x, uint8_t* stage,
+                                             TeamCtl& ctl, int buf, int empty_parity, int& held_x,
+                                             int& held_y, int lane) {
   uint64_t* full = &ctl.full[buf];
   uint64_t* empty = &ctl.empty[buf];
+  const int y0 = c.y_band + c.sb * c.sub_rows;
+  const int nr = min(c.sub_rows, c.rows - c.sb * c.sub_rows);
+  StepInfo info;
+  info.item = c.item;
+  info.roi = c.r;
+  info.y0 = y0;
+  info.nr = nr;
+  info.flags = (c.sb == 0 ? kStepFirst : 0) | (c.empty ? kStepEmpty : 0) | (c.mode << kStepModeShift);
+  info.cw = c.cw;
+  info.scx = sc_x;
   if (c.empty) {  // nothing to stage; keep the barrier protocol uniform
     if (empty_parity >= 0) mbar_wait(empty, (uint32_t)empty_parity);
     if (lane == 0) {
-      ctl.item[buf] = c.item;
+      ctl.info[buf] = info;
       mbar_expect_tx(full, 0);
     }
     return;
@@ -144,8 +186,6 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
   YPlan* plan = ctl.plan[buf];
   const size_t row_bytes = c.row_bytes;
   const uintptr_t buf_lo = c.buf_lo, buf_hi = c.buf_hi;
-  const int y0 = c.y_band + c.sb * c.sub_rows;
-  const int nr = min(c.sub_rows, c.rows - c.sb * c.sub_rows);
   const uint32_t seg = (uint32_t)c.cw * 3u;
   const int j = lane >> 1, tap = lane & 1;
   int row = -1, b0 = kCoefOne, b1 = 0;
@@ -207,10 +247,7 @@ __device__ __forceinline__ void produce_step(const Cursor& c, const CropParams& 
   for (int o = 16; o > 0; o >>= 1) tx += __shfl_xor_sync(0xffffffffu, tx, o);
 
   if (empty_parity >= 0) mbar_wait(empty, (uint32_t)empty_parity);  // consumers released the buffer
-  if (lane == 0) {
-    ctl.item[buf] = c.item;
-    if (new_roi) ctl.scx[buf] = sc_x;  // OpenCV scale_x for the consumers' x coefficients
-  }
+  if (lane == 0) ctl.info[buf] = info;
   if (copy) {
     if (bulk) {
       for (uintptr_t q = g_lo; q < a_lo; ++q) s[q - g_lo] = *reinterpret_cast<const uint8_t*>(q);
@@ -265,7 +302,7 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
   extern __shared__ __align__(128) uint8_t smem[];
   float* lut = reinterpret_cast<float*>(smem);  // [3][256][32]
   uint8_t* stage_all = smem + kLutFloats * sizeof(float);
-  TeamCtl* ctl_all = reinterpret_cast<TeamCtl*>(stage_all + (size_t)p.teams * 2 * p.stage_bytes);
+  TeamCtl* ctl_all = reinterpret_cast<TeamCtl*>(stage_all + (size_t)p.teams * kStages * p.stage_bytes);
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int team = tid / kTeamThreads, ttid = tid - team * kTeamThreads;
@@ -275,7 +312,7 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
   if (items <= 0) return;  // (the ticket words are only valid when ROI 0 exists)
   const size_t plane = (size_t)S * S;
   TeamCtl& ctl = ctl_all[team];
-  uint8_t* stage = stage_all + (size_t)team * 2 * p.stage_bytes;
+  uint8_t* stage = stage_all + (size_t)team * kStages * p.stage_bytes;
 
   // the table: 768 values, each written as one 128-byte row (a copy per bank)
   for (int i = tid; i < 3 * 256; i += blockDim.x) {
@@ -289,10 +326,11 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
     for (int k = 0; k < kLutRep / 4; ++k) row[k] = make_float4(f, f, f, f);
   }
   if (ttid == 0) {
-    mbar_init(&ctl.full[0], 1);
-    mbar_init(&ctl.full[1], 1);
-    mbar_init(&ctl.empty[0], kTeamConsumers / 32);
-    mbar_init(&ctl.empty[1], kTeamConsumers / 32);
+#pragma unroll
+    for (int b = 0; b < kStages; ++b) {
+      mbar_init(&ctl.full[b], 1);
+      mbar_init(&ctl.empty[b], kTeamConsumers / 32);
+    }
     mbar_fence_init();
   }
   __syncthreads();
@@ -300,7 +338,7 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
   if (ttid >= kTeamConsumers) {
     // =============================== producer warp ====================================
     const int n_teams = (int)gridDim.x * p.teams;
-    auto next_item = [&](int current) -> int {
+    auto draw = [&](int current) -> int {  // the next work item, or -1
       int it;
       if (p.tickets != nullptr) {
         it = lane == 0 ? atomicAdd(p.tickets, 1) : 0;
@@ -311,32 +349,33 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
       return it < items ? it : -1;
     };
     Cursor cur;
-    double sc_y = 0.0;
-    int held_x = -2, held_y = -2;
     int s = 0;
-    for (int item = next_item(-1); item >= 0; item = next_item(item)) {
-      load_item(cur, p, item);
-      held_x = held_y = -2;  // a new item starts with nothing in the consumers' registers
+    ItemRecord rec = fetch_item(p, draw(-1));
+    while (rec.item >= 0) {
+      load_item(cur, p, rec);
+      // the next ticket and its ROI record are fetched while this item is staged
+      const int next = draw(rec.item);
+      double sc_y = 0.0, sc_x = 0.0;
+      if (!cur.empty) {  // both scales at once: lane parity picks the axis
+        const double sc = axis_scale(S, (lane & 1) ? cur.cw : cur.ch);
+        sc_y = __shfl_sync(0xffffffffu, sc, 0);
+        sc_x = __shfl_sync(0xffffffffu, sc, 1);
+      }
+      int held_x = -2, held_y = -2;  // a new item starts with nothing in the consumers' registers
       for (; cur.sb < cur.nsub; ++cur.sb, ++s) {
+        const int buf = s % kStages, use = s / kStages;
         // more than 224 columns: a lane walks the step once per column chunk, so nothing carries over
         if (!kFixed224 && S > kTeamConsumers) held_x = held_y = -2;
-        const int buf = s & 1;
-        const int empty_parity = s >= 2 ? (((s >> 1) - 1) & 1) : -1;
-        double sc_x = 0.0;
-        const bool new_roi = cur.sb == 0 && !cur.empty;
-        if (new_roi) {
-          sc_y = axis_scale(S, cur.ch);
-          sc_x = axis_scale(S, cur.cw);
-        }
-        produce_step(cur, p, sc_y, stage + (size_t)buf * p.stage_bytes, ctl, buf, empty_parity, sc_x, new_roi,
+        produce_step(cur, sc_y, sc_x, stage + (size_t)buf * p.stage_bytes, ctl, buf, use ? ((use - 1) & 1) : -1,
                      held_x, held_y, lane);
+        if (cur.sb == 0) rec = fetch_item(p, next);
       }
     }
     {  // the end marker travels like a step
-      const int buf = s & 1;
-      if (s >= 2) mbar_wait(&ctl.empty[buf], (uint32_t)(((s >> 1) - 1) & 1));
+      const int buf = s % kStages, use = s / kStages;
+      if (use) mbar_wait(&ctl.empty[buf], (uint32_t)((use - 1) & 1));
       if (lane == 0) {
-        ctl.item[buf] = -1;
+        ctl.info[buf].item = -1;
         mbar_expect_tx(&ctl.full[buf], 0);
         if (p.tickets != nullptr && atomicAdd(p.tickets + 1, 1) == n_teams - 1) {
           p.tickets[0] = 0;  // every team has drawn its last ticket: leave the words as they were
@@ -353,21 +392,16 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
   uint32_t hx0 = 0, hx1 = 0, hx2 = 0, hy0 = 0, hy1 = 0, hy2 = 0;  // the two live horizontal passes
   int xo = 0;
   uint32_t coef = 0;
-  double sc_x = 0.0;  // of the current item's ROI
-  Cursor cur;
-  cur.item = -1;
   for (int s = 0;; ++s) {
-    const int buf = s & 1;
-    mbar_wait(&ctl.full[buf], (s >> 1) & 1);
-    const int item = ctl.item[buf];
-    if (item < 0) break;
-    if (item != cur.item) load_item(cur, p, item);
-    const int y0 = cur.y_band + cur.sb * cur.sub_rows;
-    const int nr = min(cur.sub_rows, cur.rows - cur.sb * cur.sub_rows);
-    float* const obase = p.out + ((size_t)cur.r * 3) * plane + (size_t)y0 * S;
-    if (cur.sb == 0 && !cur.empty) sc_x = ctl.scx[buf];
+    const int buf = s % kStages;
+    mbar_wait(&ctl.full[buf], (uint32_t)((s / kStages) & 1));
+    const int4 ia = *reinterpret_cast<const int4*>(&ctl.info[buf]);  // item roi y0 nr
+    if (ia.x < 0) break;
+    const int2 ib = *reinterpret_cast<const int2*>(&ctl.info[buf].flags);  // flags cw
+    const int nr = ia.w;
+    float* const obase = p.out + ((size_t)ia.y * 3) * plane + (size_t)ia.z * S;
 
-    if (cur.empty) {
+    if (ib.x & kStepEmpty) {
       // mobilenet_preprocess.py:266-267: a 1x1 black crop
       const float e0 = lds_f32(lut_lane), e1 = lds_f32(lut_lane + 256 * kLutRep * 4),
                   e2 = lds_f32(lut_lane + 512 * kLutRep * 4);
@@ -384,16 +418,17 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
       for (int xb = 0; xb < chunks; ++xb) {
         const int x = xb * kTeamConsumers + col0;
         const bool live = kFixed224 || x < S;
-        if (cur.sb == 0 || chunks > 1) {
+        if ((ib.x & kStepFirst) || chunks > 1) {
           // this lane's x coefficients (xofs / alpha entry), kept in registers for the whole item
+          const int mode = ib.x >> kStepModeShift;
           xo = 0, coef = 0;
           if (live) {
-            if (cur.mode == kResizeCopy) {
+            if (mode == kResizeCopy) {
               xo = x * 3, coef = kCoefOne;
-            } else if (cur.mode == kResizeBox2) {
+            } else if (mode == kResizeBox2) {
               xo = x * 6, coef = (kCoefOne / 2) | ((kCoefOne / 2) << 16);
             } else {
-              const AxisCoef k = axis_coef(x, sc_x, cur.cw, true);
+              const AxisCoef k = axis_coef(x, ctl.info[buf].scx, ib.y, true);
               xo = k.s0 * 3, coef = (uint32_t)k.w0 | ((uint32_t)k.w1 << 16);
             }
           }
@@ -420,7 +455,6 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) crop_resize_kerne
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&ctl.empty[buf]);  // this warp is done with the staging buffer + plan
-    ++cur.sb;
   }
 }
 
@@ -459,15 +493,15 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   // buffers; wide ones fewer teams with larger buffers.
   const size_t widest = ((size_t)src_w * 3 + 30 + 15) & ~(size_t)15;
   const size_t fixed = kLutFloats * sizeof(float) + kMaxTeams * sizeof(TeamCtl);
-  IA_RETURN_IF((size_t)optin < fixed + 4 * widest, IA_ERR_UNSUPPORTED);
+  IA_RETURN_IF((size_t)optin < fixed + 2 * kStages * widest, IA_ERR_UNSUPPORTED);
   const size_t avail = (size_t)optin - fixed;
-  int teams = (int)(avail / (4 * widest));
+  int teams = (int)(avail / (2 * kStages * widest));
   if (teams > kMaxTeams) teams = kMaxTeams;
-  const size_t stage = (avail / ((size_t)teams * 2)) & ~(size_t)127;
+  const size_t stage = (avail / ((size_t)teams * kStages)) & ~(size_t)127;
   IA_RETURN_IF(stage >= (1u << 20), IA_ERR_UNSUPPORTED);
   c.teams = teams;
   c.stage_bytes = (int)stage;
-  const size_t smem = kLutFloats * sizeof(float) + (size_t)teams * 2 * stage + (size_t)teams * sizeof(TeamCtl);
+  const size_t smem = kLutFloats * sizeof(float) + (size_t)teams * kStages * stage + (size_t)teams * sizeof(TeamCtl);
   void (*kernel)(CropParams) = out_size == 224 ? crop_resize_kernel<true> : crop_resize_kernel<false>;
   e = allow_max_dynamic_smem(reinterpret_cast<const void*>(kernel));
   if (e != cudaSuccess) return (int)e;
