@@ -384,20 +384,10 @@ extern "C" int ia_classify_topk(const float* logits_dev, int rows, int classes, 
   int warps = (int)(kClassifySmemBudget / row_bytes);
   warps = warps < 1 ? 1 : (warps > kClassifyMaxWarps ? kClassifyMaxWarps : warps);
   const size_t smem = row_bytes * warps;
-  if (smem > 48 * 1024) {
-    static thread_local int raised_for = -1;  // per device, per thread: the attribute is sticky
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
+  if (smem > 48 * 1024) {  // once per (kernel, device), always to the same largest value
+    cudaError_t e = allow_max_dynamic_smem(reinterpret_cast<const void*>(classify_topk_kernel<true>));
+    if (e == cudaSuccess) e = allow_max_dynamic_smem(reinterpret_cast<const void*>(classify_topk_kernel<false>));
     if (e != cudaSuccess) return (int)e;
-    if (raised_for != dev) {
-      e = cudaFuncSetAttribute(classify_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)kClassifySmemLimit);
-      if (e != cudaSuccess) return (int)e;
-      e = cudaFuncSetAttribute(classify_topk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)kClassifySmemLimit);
-      if (e != cudaSuccess) return (int)e;
-      raised_for = dev;
-    }
   }
   p.warps = warps;
   const int blocks = (rows + warps - 1) / warps;

@@ -46,7 +46,10 @@ inline cudaError_t allow_max_dynamic_smem(const void* kernel) {
   int optin = 0;
   e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+  cudaFuncAttributes attr;  // static shared memory counts against the same limit
+  e = cudaFuncGetAttributes(&attr, kernel);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)attr.sharedSizeBytes);
   if (e == cudaSuccess) flag = true;
   return e;
 }
@@ -68,6 +71,12 @@ __device__ __forceinline__ void mbar_fence_init() {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
                "r"(bytes)
+               : "memory");
+}
+
+// raise the barrier's pending transaction count without arriving (the arrival comes separately)
+__device__ __forceinline__ void mbar_add_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
 
@@ -194,6 +203,11 @@ __device__ __forceinline__ void load6(const uint32_t* stage32, int a, uint32_t& 
 __device__ __forceinline__ uint32_t tap_pair(uint32_t lo, uint32_t hi, int c) {
   return __byte_perm(lo, hi, c == 0 ? 0x30u : (c == 1 ? 0x41u : 0x52u));
 }
+
+// K1's general linear resize runs in the tile kernel K4 uses (ia_resize_tiles.cuh, compiled in
+// ia_crop.cu): n equally sized frames -> letterboxed float32 [n, 3, target, target] = v / divisor.
+int launch_letterbox_tiles(const uint8_t* frames, int n, int src_h, int src_w, int target, int new_h, int new_w,
+                           int pad_h, int pad_w, float divisor, uint32_t pad_rgb, float* out, cudaStream_t stream);
 
 // numpy.maximum / numpy.minimum propagate NaN; fmaxf/fminf do not.
 __device__ __forceinline__ float np_max(float a, float b) { return (a != a) ? a : ((b != b) ? b : fmaxf(a, b)); }

@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(kRoiThreads) roi_rects_kernel(const RoiParams 
 
 }  // namespace ia
 
-#include "ia_crop_resize.cuh"  // stage B: crop_resize_kernel, launch_crops
+#include "ia_resize_tiles.cuh"  // stage B: resize_tiles_kernel, launch_crops (+ K1's linear mode)
 
 namespace ia {
 

@@ -574,7 +574,7 @@ extern "C" int ia_decode_nms(const float* head_dev, int layout, int n, int ancho
     const long long blocks = (long long)d.tiles * n;
     IA_RETURN_IF(blocks > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
     const size_t smem = (size_t)tile * d.row_floats * 4 + 16;
-    e = cudaFuncSetAttribute(decode_filter_v5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = allow_max_dynamic_smem(reinterpret_cast<const void*>(decode_filter_v5_kernel));
     if (e != cudaSuccess) return (int)e;
     decode_filter_v5_kernel<<<(unsigned)blocks, kDecodeThreads, smem, stream>>>(d);
     q.image_stride = (size_t)anchors * d.row_floats;

@@ -149,8 +149,12 @@ __device__ __forceinline__ void letterbox_body(const PreParams& p, const uint8_t
     const int leader = __ffs(same) - 1;
     const bool copy = (leader == lane) && row >= 0;
     const unsigned leaders = __ballot_sync(0xffffffffu, copy);
-    const int slot = __popc(leaders & ((1u << leader) - 1u));
-    if (row >= 0 && slot >= p.slots_cap) __trap();  // host and device tables disagree: never expected
+    const int slot_raw = __popc(leaders & ((1u << leader) - 1u));
+    // The host sized the staging buffer from the same tables (IEEE twins of this code), so a row
+    // beyond it is not expected; if the two ever disagreed the row would share the last slot —
+    // wrong pixels in this row group, never an access outside the buffer and never a trap that
+    // would take the caller's CUDA context down.
+    const int slot = min(slot_raw, p.slots_cap - 1);
     const uint8_t* g = frame + (size_t)max(row, 0) * row_bytes;
     const uint32_t mis = (uint32_t)((uintptr_t)g & 15);
     const int off = slot * p.slot_bytes + (int)mis;
@@ -362,7 +366,8 @@ static int max_distinct_rows(int mode, int rows, const ia_letterbox_geom& g, dou
 
 // Geometry, mode, rows per CTA and staging size for one frame shape (cached: the table walk
 // costs tens of microseconds on the host).
-static int plan_letterbox(int src_h, int src_w, int target, PreParams& p, int& mode, size_t& smem) {
+static int plan_letterbox(int src_h, int src_w, int target, PreParams& p, int& mode, size_t& smem,
+                          bool linear_in_tile_kernel = false) {
   ia_letterbox_geom g;
   int rc = ia_letterbox_geometry(src_h, src_w, target, &g);
   if (rc != IA_OK) return rc;
@@ -406,6 +411,7 @@ static int plan_letterbox(int src_h, int src_w, int target, PreParams& p, int& m
     }
   }
   smem = (size_t)slots * p.slot_bytes + xtab_bytes;
+  if (linear_in_tile_kernel && mode == kResizeLinear) return IA_OK;  // geometry and mode only
   IA_RETURN_IF(smem > 200 * 1024, IA_ERR_UNSUPPORTED);
   IA_RETURN_IF((size_t)slots * src_w * 3 >= (1u << 20), IA_ERR_UNSUPPORTED);  // mbarrier tx range
   p.rows_per_cta = rows;
@@ -427,7 +433,7 @@ static int launch_planned(PreParams& p, int mode, size_t smem, int n, const PreR
     case kResizeGather: kernel = letterbox_kernel<kOutU8, kResizeGather, kRagged>; break;
     default: kernel = letterbox_kernel<kOutU8, kResizeLinear, kRagged>; break;
   }
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = allow_max_dynamic_smem(reinterpret_cast<const void*>(kernel));
   if (e != cudaSuccess) return (int)e;
   kernel<<<(unsigned)blocks, kPreThreads, smem, stream>>>(p, rg);
   return launch_status();
@@ -442,8 +448,11 @@ static int launch_letterbox(const uint8_t* frames, int n, int src_h, int src_w, 
   PreParams p;
   int mode;
   size_t smem;
-  int rc = plan_letterbox(src_h, src_w, target, p, mode, smem);
+  int rc = plan_letterbox(src_h, src_w, target, p, mode, smem, !kOutU8);
   if (rc != IA_OK) return rc;
+  if (!kOutU8 && mode == kResizeLinear)  // the separable tile kernel (ia_resize_tiles.cuh)
+    return launch_letterbox_tiles(frames, n, src_h, src_w, target, p.new_h, p.new_w, p.pad_h, p.pad_w, divisor,
+                                  pad_rgb, static_cast<float*>(out), stream);
   p.frames = frames;
   p.out = out;
   p.divisor = divisor;
@@ -492,8 +501,7 @@ static int launch_letterbox_ragged(const ia_frame_desc* frames, int n, int targe
       IA_RETURN_IF(ctas > 0x7fffffffLL, IA_ERR_UNSUPPORTED);
     }
     mp.first_cta[mp.num_shapes] = (int)ctas;
-    cudaError_t e = cudaFuncSetAttribute(letterbox_mixed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem_max);
+    cudaError_t e = allow_max_dynamic_smem(reinterpret_cast<const void*>(letterbox_mixed_kernel));
     if (e != cudaSuccess) return (int)e;
     letterbox_mixed_kernel<<<(unsigned)ctas, kPreThreads, smem_max, stream>>>(mp);
     return launch_status();

@@ -90,11 +90,16 @@ def letterbox_batch_cuda(frames: torch.Tensor, target: int, color=(114, 114, 114
 
 
 # -------------------------------------------------------------------------------- K2 + K3
+NMS_MAX_CLASSES = 1023  # class ids 0..1022: the sort key holds a class in 10 bits (csrc kMaxClasses)
 _workspaces: dict[tuple[int, int], torch.Tensor] = {}
 
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    key = (device.index if device.index is not None else torch.cuda.current_device(), 0)
+    """Default candidate-list scratch: one buffer per (device, current torch stream), so calls
+    issued on different streams (or from threads with different current streams) never share
+    the counters and key lists.  Calls on ONE stream reuse it in stream order."""
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    key = (index, int(torch.cuda.current_stream(index).cuda_stream))
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)

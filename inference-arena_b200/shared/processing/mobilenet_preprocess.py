@@ -87,14 +87,18 @@ class MobileNetPreprocessor:
 
 def extract_crop(image: np.ndarray, box: np.ndarray) -> np.ndarray:
     """Copy the region ``box[:4] = [x1, y1, x2, y2]`` (truncated toward zero, clamped to the
-    frame) out of ``image``; an empty region yields ``zeros((1, 1, 3))``.  The rectangle
-    arithmetic runs on the device (the code the fused K4 kernel uses); the pixels of a host
-    image are then a plain host-side slice copy — moving the whole frame to the GPU and back
-    just to copy a window of it would only add PCIe traffic."""
+    frame) out of ``image``; an empty region yields ``zeros((1, 1, 3))``.
+
+    The four coordinates are truncated on the host in the caller's own dtype, exactly as the
+    reference's ``map(int, box[:4])`` does (mobilenet_preprocess.py:256): a float64 99.99999999
+    stays 99, integer boxes pass through, NaN / inf raise what ``int()`` raises.  (Device-resident
+    float32 boxes take ``extract_crop_rects_cuda`` / the fused K4 kernel instead.)  The pixels
+    of a host image are then a plain host-side slice copy — moving the whole frame to the GPU
+    and back just to copy a window of it would only add PCIe traffic."""
     height, width = image.shape[:2]
-    row = np.asarray(box[:4], dtype=np.float64).astype(np.float32).reshape(1, 4)
-    rect = _hostio.to_host(_dev.extract_crop_rects_cuda(_hostio.to_device(row), height, width))[0]
-    _, x1, y1, x2, y2, empty = (int(v) for v in rect[:6])
-    if empty:
+    left, top, right, bottom = (int(v) for v in box[:4])
+    left, top = max(left, 0), max(top, 0)
+    right, bottom = min(right, width), min(bottom, height)
+    if right <= left or bottom <= top:
         return np.zeros((1, 1, 3), dtype=np.uint8)
-    return image[y1:y2, x1:x2].copy()
+    return image[top:bottom, left:right].copy()

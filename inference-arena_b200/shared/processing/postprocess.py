@@ -43,13 +43,21 @@ def parse_yolo_output(raw_output: np.ndarray, confidence_threshold: float,
 def apply_nms(boxes: np.ndarray, scores: np.ndarray, class_ids: np.ndarray, conf_threshold: float,
               iou_threshold: float) -> list[int]:
     """Class-aware NMS on ``[N,4]`` cx,cy,w,h boxes; returns the indices to keep
-    (class-ascending, score-descending)."""
+    (class-ascending, score-descending).
+
+    The reference groups with ``np.unique(class_ids)`` (postprocess.py:116), so any integer ids
+    work there; the device key holds a class in 10 bits.  The ids are therefore renumbered
+    densely in ascending order first (order-preserving, so the output order is unchanged)."""
     m = int(len(scores))
     if m == 0:
         return []
+    _, dense = np.unique(np.asarray(class_ids), return_inverse=True)
+    dense = dense.reshape(-1)
+    if int(dense.max()) >= _dev.NMS_MAX_CLASSES:
+        raise ValueError(f"apply_nms: more than {_dev.NMS_MAX_CLASSES} distinct class ids")
     keep, count, _ = _dev.nms_cuda(_hostio.to_device(np.asarray(boxes, dtype=np.float32)),
                                    _hostio.to_device(np.asarray(scores, dtype=np.float32)),
-                                   _hostio.to_device(np.asarray(class_ids).astype(np.int32)),
+                                   _hostio.to_device(dense.astype(np.int32)),
                                    conf_threshold, iou_threshold, max_det=m)
     k = int(count[0].item())
     return [int(v) for v in _hostio.to_host(keep[:k])]
