@@ -44,7 +44,7 @@ namespace ia {
 constexpr int kTeamConsumers = 224;
 constexpr int kTeamThreads = kTeamConsumers + 32;
 constexpr int kMaxTeams = 4;
-constexpr int kTileRows = 28;  // output rows of one tile: one producer lane per row
+constexpr int kTileRows = 28;  // most output rows of one tile: one producer lane per row
 constexpr int kStages = 2;     // staging buffers per team
 constexpr int kLutRep = 32;    // one copy of the 3x256 table per bank
 constexpr int kLutFloats = 3 * 256 * kLutRep;
@@ -64,7 +64,8 @@ struct TileParams {
   int out_w, out_h;
   int canvas, canvas_x0, canvas_y0;  // canvas edge (S or T), position of the resized image in it
   int tiles_x, tiles_y;              // image tiles per image
-  int fill_top, fill_bottom;         // fill tiles (bands of kTileRows rows) above / below
+  int tile_rows;                     // output rows per tile (<= kTileRows)
+  int fill_top, fill_bottom;         // fill tiles (bands of tile_rows rows) above / below
   int fill_left, fill_right;         // 1 when there is padding left / right of the image
   int tiles_per_image;
   uint32_t fill_rgb;  // table indices of the fill colour, r | g << 8 | b << 16
@@ -74,6 +75,10 @@ struct TileParams {
   // Work distribution.  With `tickets` (two zeroed ints: next tile, teams finished) a team draws
   // its tiles one at a time; the last team to finish zeroes both again.  Without, teams stride.
   int* tickets;
+  // ---- whole frames (rois == null): one resize geometry for the launch, so OpenCV's scales come
+  // from the host and the x coefficients of every column are tabulated once per CTA
+  double sc_x, sc_y;
+  int xtab_bytes;  // out_w * 8 (16-byte multiple) or 0
   // ---- output values: ((v/255) - mean) / std per channel, or v / divisor when divisor != 0
   float divisor;
   float mean[3], stdv[3];
@@ -173,8 +178,8 @@ __device__ __forceinline__ void load_tile(Cursor& c, const TileParams& p, const 
   int cy, cx;  // canvas position of the tile
   if (local < n_image_tiles) {
     const int ty = local / p.tiles_x, tx = local - ty * p.tiles_x;
-    c.y_first = ty * kTileRows;
-    c.rows = min(kTileRows, p.out_h - c.y_first);
+    c.y_first = ty * p.tile_rows;
+    c.rows = min(p.tile_rows, p.out_h - c.y_first);
     c.x0 = tx * kTeamConsumers;
     c.cols = min(kTeamConsumers, p.out_w - c.x0);
     cy = p.canvas_y0 + c.y_first;
@@ -213,16 +218,16 @@ __device__ __forceinline__ void load_tile(Cursor& c, const TileParams& p, const 
       const bool below = local >= p.fill_top;
       const int k = below ? local - p.fill_top : local;
       const int lo = below ? p.canvas_y0 + p.out_h : 0, hi = below ? T : p.canvas_y0;
-      cy = lo + k * kTileRows;
-      c.rows = min(kTileRows, hi - cy);
+      cy = lo + k * p.tile_rows;
+      c.rows = min(p.tile_rows, hi - cy);
       cx = 0;
       c.cols = T;
     } else {  // columns left / right of one band of image rows
       local -= p.fill_top + p.fill_bottom;
       const bool right = p.fill_left ? local >= p.tiles_y : true;
       const int ty = (p.fill_left && right) ? local - p.tiles_y : local;
-      cy = p.canvas_y0 + ty * kTileRows;
-      c.rows = min(kTileRows, p.out_h - ty * kTileRows);
+      cy = p.canvas_y0 + ty * p.tile_rows;
+      c.rows = min(p.tile_rows, p.out_h - ty * p.tile_rows);
       cx = right ? p.canvas_x0 + p.out_w : 0;
       c.cols = right ? T - cx : p.canvas_x0;
     }
@@ -420,6 +425,7 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kern
   float* lut = reinterpret_cast<float*>(smem);  // [3][256][32]
   uint8_t* stage_all = smem + kLutFloats * sizeof(float);
   TeamCtl* ctl_all = reinterpret_cast<TeamCtl*>(stage_all + (size_t)p.teams * kStages * p.stage_bytes);
+  int2* xtab = reinterpret_cast<int2*>(ctl_all + p.teams);  // [out_w] (xofs, a0 | a1 << 16) when xtab_bytes
 
   const int tid = threadIdx.x, lane = tid & 31;
   // Warps 0 .. 7*teams-1 are the consumers (seven per team), the last `teams` warps the producers:
@@ -453,6 +459,13 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kern
     float4* row = reinterpret_cast<float4*>(lut + (size_t)i * kLutRep);
 #pragma unroll
     for (int k = 0; k < kLutRep / 4; ++k) row[k] = make_float4(f, f, f, f);
+  }
+  if (p.xtab_bytes) {
+    const int mode = resize_mode(p.src_h, p.src_w, p.out_h, p.out_w);
+    for (int x = tid; x < p.out_w; x += blockDim.x) {
+      const AxisCoef k = x_entry(mode, x, p.sc_x, p.src_w);
+      xtab[x] = make_int2(k.s0, k.w0 | (k.w1 << 16));
+    }
   }
   if (producer && lane == 0) {
 #pragma unroll
@@ -490,11 +503,19 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kern
       unsigned fills_x = 0, fills_y = 0;
       if (!cur.fill) {
         // both scales at once (lane parity picks the axis), then the tile's first and last xofs
-        const double sc = axis_scale((lane & 1) ? p.out_w : p.out_h, (lane & 1) ? cur.cw : cur.ch);
-        const double sc_y = __shfl_sync(0xffffffffu, sc, 0);
-        sc_x = __shfl_sync(0xffffffffu, sc, 1);
+        double sc_y;
+        if (p.xtab_bytes) {
+          sc_y = p.sc_y;
+          sc_x = p.sc_x;
+        } else {
+          const double sc = axis_scale((lane & 1) ? p.out_w : p.out_h, (lane & 1) ? cur.cw : cur.ch);
+          sc_y = __shfl_sync(0xffffffffu, sc, 0);
+          sc_x = __shfl_sync(0xffffffffu, sc, 1);
+        }
         if (p.tiles_x == 1) {  // the tile spans the whole width: stage whole source rows
           size_tile(cur, 0, cur.cw - 1);
+        } else if (p.xtab_bytes) {
+          size_tile(cur, xtab[cur.x0].x, xtab[cur.x0 + cur.cols - 1].x);
         } else {
           const int s0 = x_entry(cur.mode, (lane & 1) ? cur.x0 + cur.cols - 1 : cur.x0, sc_x, cur.cw).s0;
           size_tile(cur, __shfl_sync(0xffffffffu, s0, 0), __shfl_sync(0xffffffffu, s0, 1));
@@ -558,12 +579,24 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kern
       const float e0 = lds_f32(lut_lane + (rgb & 0xff) * (kLutRep * 4)),
                   e1 = lds_f32(lut_lane + (256 + ((rgb >> 8) & 0xff)) * (kLutRep * 4)),
                   e2 = lds_f32(lut_lane + (512 + ((rgb >> 16) & 0xff)) * (kLutRep * 4));
-      for (int x = col; x < ia.w; x += kTeamConsumers) {
-        float* o = obase + x;
-        for (int j = 0; j < nr; ++j, o += T) {
-          st_stream_f1(o, e0);
-          st_stream_f1(o + plane, e1);
-          st_stream_f1(o + 2 * plane, e2);
+      if (((ia.w | T) & 3) == 0 && (reinterpret_cast<uintptr_t>(obase) & 15) == 0) {
+        // whole rows of padding: 128-bit stores, a warp writes 512 contiguous bytes per plane
+        for (int x = col * 4; x < ia.w; x += kTeamConsumers * 4) {
+          float* o = obase + x;
+          for (int j = 0; j < nr; ++j, o += T) {
+            st_stream_f4(o, e0, e0, e0, e0);
+            st_stream_f4(o + plane, e1, e1, e1, e1);
+            st_stream_f4(o + 2 * plane, e2, e2, e2, e2);
+          }
+        }
+      } else {
+        for (int x = col; x < ia.w; x += kTeamConsumers) {
+          float* o = obase + x;
+          for (int j = 0; j < nr; ++j, o += T) {
+            st_stream_f1(o, e0);
+            st_stream_f1(o + plane, e1);
+            st_stream_f1(o + 2 * plane, e2);
+          }
         }
       }
     } else {
@@ -571,7 +604,11 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kern
       if (ia.z & kStepFirst) {
         // this lane's x coefficients (xofs / alpha entry), kept in registers for the whole tile
         xo = 0, coef = 0;
-        if (live) {
+        if (live && p.xtab_bytes) {
+          const int2 e = xtab[info.x0 + col];
+          xo = (e.x - info.seg_x0) * 3;
+          coef = (uint32_t)e.y;
+        } else if (live) {
           const AxisCoef k = x_entry(ia.z >> kStepModeShift, info.x0 + col, info.scx, info.cw);
           xo = (k.s0 - info.seg_x0) * 3;
           coef = (uint32_t)k.w0 | ((uint32_t)k.w1 << 16);
@@ -615,7 +652,7 @@ static int launch_tiles(TileParams& c, int widest_cols, cudaStream_t stream) {
   // at least two of the widest row segments) and a control block.  Narrow sources get four teams
   // of ~16 KB buffers; wide ones fewer teams with larger buffers.
   const size_t widest = ((size_t)widest_cols * 3 + 30 + 15) & ~(size_t)15;
-  const size_t fixed = kLutFloats * sizeof(float) + kMaxTeams * sizeof(TeamCtl);
+  const size_t fixed = kLutFloats * sizeof(float) + kMaxTeams * sizeof(TeamCtl) + (size_t)c.xtab_bytes;
   IA_RETURN_IF((size_t)optin < fixed + 2 * kStages * widest, IA_ERR_UNSUPPORTED);
   const size_t avail = (size_t)optin - fixed;
   int teams = (int)(avail / (2 * kStages * widest));
@@ -624,7 +661,8 @@ static int launch_tiles(TileParams& c, int widest_cols, cudaStream_t stream) {
   IA_RETURN_IF(stage >= (1u << 20), IA_ERR_UNSUPPORTED);
   c.teams = teams;
   c.stage_bytes = (int)stage;
-  const size_t smem = kLutFloats * sizeof(float) + (size_t)teams * kStages * stage + (size_t)teams * sizeof(TeamCtl);
+  const size_t smem = kLutFloats * sizeof(float) + (size_t)teams * kStages * stage + (size_t)teams * sizeof(TeamCtl) +
+                      (size_t)c.xtab_bytes;
   void (*kernel)(TileParams) = c.canvas == 224   ? resize_tiles_kernel<224>
                                : c.canvas == 640 ? resize_tiles_kernel<640>
                                                  : resize_tiles_kernel<0>;
@@ -655,10 +693,13 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   c.out_w = c.out_h = c.canvas = out_size;
   c.canvas_x0 = c.canvas_y0 = 0;
   c.tiles_x = (out_size + kTeamConsumers - 1) / kTeamConsumers;
+  c.tile_rows = kTileRows;
   c.tiles_y = (out_size + kTileRows - 1) / kTileRows;
   c.fill_top = c.fill_bottom = c.fill_left = c.fill_right = 0;
   c.tiles_per_image = c.tiles_x * c.tiles_y;
   c.fill_rgb = 0;
+  c.sc_x = c.sc_y = 0.0;
+  c.xtab_bytes = 0;
   c.divisor = 0.f;
   for (int i = 0; i < 3; ++i) {
     c.mean[i] = mean[i];
@@ -690,12 +731,25 @@ int launch_letterbox_tiles(const uint8_t* frames, int n, int src_h, int src_w, i
   c.canvas_x0 = pad_w;
   c.canvas_y0 = pad_h;
   c.tiles_x = (new_w + kTeamConsumers - 1) / kTeamConsumers;
-  c.tiles_y = (new_h + kTileRows - 1) / kTileRows;
-  c.fill_top = (pad_h + kTileRows - 1) / kTileRows;
-  c.fill_bottom = (target - pad_h - new_h + kTileRows - 1) / kTileRows;
+  // Tiles are dealt round-robin (no scratch memory for tickets here): a small batch takes shorter
+  // tiles so that every team still gets a dozen of them
+  int sms = 148;
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  c.tile_rows = kTileRows;
+  while (c.tile_rows > 7 && (long long)n * c.tiles_x * ((target + c.tile_rows - 1) / c.tile_rows) < 12LL * kMaxTeams * sms)
+    c.tile_rows /= 2;
+  c.tiles_y = (new_h + c.tile_rows - 1) / c.tile_rows;
+  c.fill_top = (pad_h + c.tile_rows - 1) / c.tile_rows;
+  c.fill_bottom = (target - pad_h - new_h + c.tile_rows - 1) / c.tile_rows;
   c.fill_left = pad_w > 0;
   c.fill_right = target - pad_w - new_w > 0;
   c.tiles_per_image = c.tiles_x * c.tiles_y + c.fill_top + c.fill_bottom + (c.fill_left + c.fill_right) * c.tiles_y;
+  c.sc_x = axis_scale(new_w, src_w);
+  c.sc_y = axis_scale(new_h, src_h);
+  c.xtab_bytes = (new_w * 8 + 15) & ~15;
   c.fill_rgb = pad_rgb;
   c.divisor = divisor;
   for (int i = 0; i < 3; ++i) c.mean[i] = 0.f, c.stdv[i] = 1.f;
