@@ -68,12 +68,18 @@ _W = {}
 
 def _cpu_worker_init(images: int, seed_base: int) -> None:
     """Each worker owns `images` synthetic requests; cv2 single-threaded per worker
-    (BASELINE.md §3 mode ii: one process per host core)."""
+    (BASELINE.md §3 mode ii: one process per host core).  The worker runs the reference's own
+    modules when they are staged (baseline/_ref), else the oracle port of them."""
     import cv2
 
     from workloads import synth
 
     cv2.setNumThreads(1)
+    try:
+        from oracle import refrun
+        _W["reference"] = refrun.Reference()
+    except Exception:
+        _W["reference"] = None
     seed = seed_base + os.getpid() % 100000
     _W["frames"] = synth.frames(images, SRC_H, SRC_W, seed=seed)
     _W["heads"] = synth.head_v5(images, seed=seed + 1)
@@ -82,11 +88,15 @@ def _cpu_worker_init(images: int, seed_base: int) -> None:
 def _cpu_worker_step(reps: int):
     from oracle import pipeline as O
 
+    ref = _W.get("reference")
     t0 = time.perf_counter()
     done = 0
     for _ in range(reps):
         for f, h in zip(_W["frames"], _W["heads"]):
-            O.run_image(f, h, CONF, IOU, resize=O.cv2_resize)
+            if ref is not None:
+                ref.run_image(f, h, CONF, IOU)
+            else:
+                O.run_image(f, h, CONF, IOU, resize=O.cv2_resize)
             done += 1
     return done, time.perf_counter() - t0
 
@@ -100,6 +110,8 @@ class CpuArm:
 
         self.cores = len(os.sched_getaffinity(0))
         self.images_per_worker = images_per_worker
+        from oracle import refrun
+        self.reference_root = refrun.find_reference()
         ctx = mp.get_context("fork")
         self.pool = ctx.Pool(self.cores, initializer=_cpu_worker_init, initargs=(images_per_worker, 1000))
 
@@ -117,10 +129,16 @@ class CpuArm:
         import cv2
         import numpy as np
 
-        return {"value": images / wall, "unit": UNIT, "cores": self.cores, "kind": "port",
+        if self.reference_root is not None:
+            kind, what = "reference", (f"the reference's own modules from {self.reference_root.name} "
+                                       "(YOLOPreprocessor, curator.py:295-304 decode restated + its apply_nms, "
+                                       "scale_boxes, extract_crop, MobileNetPreprocessor) via oracle/refrun.py")
+        else:
+            kind, what = "port", "oracle/pipeline.py run_image with cv2.resize (reference files not staged)"
+        return {"value": images / wall, "unit": UNIT, "cores": self.cores, "kind": kind,
                 "sample": f"{images} requests of the same C5 workload (1080p frame + 25200x85 head -> full chain) "
                           f"in {wall:.2f} s wall over {self.cores} processes, cv2 {cv2.__version__} (1 thread each), "
-                          f"numpy {np.__version__}; oracle/pipeline.py run_image with cv2.resize"}
+                          f"numpy {np.__version__}; {what}"}
 
 
 def run_reference_arm(args) -> None:
@@ -144,8 +162,8 @@ def run_reference_arm(args) -> None:
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall_total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f32",
-        "data": "synthetic", "config": workload_config(arm.cores * 4 * reps, 1) | {"cpu_step": f"{arm.cores * 4 * reps} images/step"},
-        "cpu_baseline": arm_desc | {"value": value},
+        "data": "synthetic", "config": workload_config(args.batch, args.gpus),
+        "cpu_baseline": arm_desc | {"value": value, "cpu_step": f"{arm.cores * 4 * reps} requests per timed step"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -154,7 +172,7 @@ def run_reference_arm(args) -> None:
 
 # ============================================================================== GPU arm
 def synth_inputs_device(batch: int, dev, seed: int):
-    """Device-side twin of oracle/synth.py (frames: uniform noise; heads: low-confidence
+    """Device-side twin of workloads/synth.py (frames: uniform noise; heads: low-confidence
     background + k in {3,4,5} planted objects x 30 jittered anchors per image)."""
     import torch
 
@@ -199,7 +217,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "10"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
 
@@ -269,6 +287,22 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
     out["C2_preprocess_64x640x480"] = {"images_per_s": 64 / ms * 1e3, "ms": ms, "algorithmic_bytes": by,
                                        "achieved_gbs": by / ms / 1e6, "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
     del sets, outs
+    # ---- K1's general linear mode on the shapes COCO actually has: 500x375 (upscale to 640x480)
+    # and 1024x768 (downscale), 64 frames each; algorithmic bytes per SURVEY 8d
+    for name, h, w in (("K1_linear_up_64x500x375", 375, 500), ("K1_linear_down_64x1024x768", 768, 1024)):
+        sets = [torch.randint(0, 256, (64, h, w, 3), dtype=torch.uint8, device=dev) for _ in range(4)]
+        outs = [torch.empty((64, 3, 640, 640), dtype=torch.float32, device=dev) for _ in range(2)]
+        it["i"] = 0
+
+        def k1_linear():
+            i = it["i"] = it["i"] + 1
+            D.preprocess_batch_cuda(sets[i % 4], 640, out=outs[i % 2])
+
+        ms = time_loop(k1_linear, steps, warmup, dev)
+        by = 64 * (h * w * 3 + 3 * 640 * 640 * 4)
+        out[name] = {"images_per_s": 64 / ms * 1e3, "ms": ms, "algorithmic_bytes": by,
+                     "achieved_gbs": by / ms / 1e6, "frac_of_hbm_peak": by / ms / 1e6 / peak_gbs}
+        del sets, outs
     # ---- C3: 256 heads -> K2+K3
     _, head = synth_inputs_device(256, dev, seed=2)
     ws = torch.empty(D.lib().ia_decode_nms_workspace_bytes(256, ANCHORS, 4096), dtype=torch.uint8, device=dev)
@@ -431,8 +465,16 @@ def run_gpu_arm(args) -> None:
     pipe = DevicePipeline(B, SRC_H, SRC_W, dev, max_det=32, max_candidates=4096, rois_per_image=8)
 
     # ---------------- device-resident throughput (`value`) + per-kernel events -----------
-    for _ in range(args.warmup):
+    # the clock sampler runs from before the warm-up to the end of the timed region; the warm-up
+    # (the same steps, untimed) lasts at least 0.4 s so that a 10 ms sampler sees the load
+    sampler = ClockSampler(local) if rank == 0 else None
+    t_warm = time.perf_counter()
+    done = 0
+    while done < args.warmup or time.perf_counter() - t_warm < 0.4:
         out = pipe.run(frames, head)
+        done += 1
+        if done % 16 == 0:
+            torch.cuda.synchronize(dev)
     torch.cuda.synchronize(dev)
     assert int(out.status.max()) == 0, "synthetic workload overflowed the candidate/detection budget"
     total_rois = int(out.roi_offsets[-1])
@@ -440,7 +482,6 @@ def run_gpu_arm(args) -> None:
     crop_px = int(((rois_np[:, 3] - rois_np[:, 1]) * (rois_np[:, 4] - rois_np[:, 2]) * (1 - rois_np[:, 5])
                    + rois_np[:, 5]).sum())
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
-    sampler = ClockSampler(local) if rank == 0 else None
     barrier()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
@@ -462,6 +503,15 @@ def run_gpu_arm(args) -> None:
     kernels = {k: {"ms": k_ms[k], "algorithmic_bytes": k_bytes[k], "achieved_gbs": k_bytes[k] / k_ms[k] / 1e6,
                    "frac": k_bytes[k] / k_ms[k] / 1e6 / peak_gbs, "share_of_step": k_ms[k] / sum(k_ms.values())}
                for k in k_ms}
+    # K1 at 1080p is a 3x gather: it reads only the source rows it needs (one in three), so the
+    # algorithmic figure above exceeds the HBM peak; the bytes it physically moves are the honest
+    # roofline fraction (the ncu DRAM counters in profiles/ agree with this count)
+    g = D.letterbox_geometry(SRC_H, SRC_W, 640)
+    if SRC_H == 3 * g.new_h and SRC_W == 3 * g.new_w:
+        k1 = kernels["K1_letterbox_normalize_chw"]
+        k1["physical_bytes"] = B * (g.new_h * SRC_W * 3 + 3 * 640 * 640 * 4)
+        k1["frac_physical"] = k1["physical_bytes"] / k1["ms"] / 1e6 / peak_gbs
+        k1["note"] = "frac = algorithmic bytes (SURVEY 8d) / time / peak; frac_physical counts only the source rows the 3x gather reads"
     dom = max(k_ms, key=k_ms.get)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak_gbs,
                 "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
@@ -517,36 +567,36 @@ def run_gpu_arm(args) -> None:
     h2d = B * hp.h2d_bytes_per_image
     d2h = hp.d2h_bytes(B)
 
-    if rank != 0:
-        if world > 1:
-            dist.barrier()
-            dist.destroy_process_group()
-        return
-
     # ---------------- the same leg with the frames arriving as JPEG files ----
     # What the services actually receive.  Extra information, not the `e2e` key: the boundary
     # moves one step earlier (the reference decodes with cv2 on the host before the path).
+    # Every rank runs these legs (they move 0.8 MB per image instead of 14.8 MB: the legs that
+    # can scale on a host whose copy bandwidth is shared); times are the max over ranks.
+    def timed_leg(pipe_, src_, heads_, **kw):
+        for _ in range(2):
+            r = pipe_.run(src_, heads_, **kw)
+        barrier()
+        t0.record()
+        tk = None
+        for _ in range(e2e_steps):
+            nx = pipe_.submit(src_, heads_, **kw)
+            if tk is not None:
+                r = tk.wait()
+            tk = nx
+        r = tk.wait()
+        t1.record()
+        barrier()
+        assert int(r["status"].max()) == 0
+        return max_over_ranks(t0.elapsed_time(t1))
+
     e2e_jpeg = None
-    if world == 1 and not args.no_stages:
+    if not args.no_stages:
         try:
             from workloads import jpeg_cases as W
             files = [W.encode(W.photo(SRC_H, SRC_W, seed=i), 90, "420") for i in range(8)]
             blobs = [files[i % 8] for i in range(B)]
-            for _ in range(2):
-                res = hp.run(blobs, h_heads)
-            t0.record()
-            ticket = None
-            for _ in range(e2e_steps):
-                nxt = hp.submit(blobs, h_heads)
-                if ticket is not None:
-                    res = ticket.wait()
-                ticket = nxt
-            res = ticket.wait()
-            t1.record()
-            torch.cuda.synchronize(dev)
-            jm = t0.elapsed_time(t1)
-            assert int(res["status"].max()) == 0
-            e2e_jpeg = {"value": B * e2e_steps / (jm / 1e3), "unit": UNIT, "h2d_bytes_per_step": hp.last_h2d_bytes,
+            jm = timed_leg(hp, blobs, h_heads)
+            e2e_jpeg = {"value": world * B * e2e_steps / (jm / 1e3), "unit": UNIT, "h2d_bytes_per_step": hp.last_h2d_bytes,
                         "d2h_bytes_per_step": hp.d2h_bytes(B), "ms_per_step": jm / e2e_steps,
                         "jpeg_kb_per_frame": sum(map(len, files)) / 8 / 1024,
                         "api": "HostPipeline.submit(list_of_jpeg_bytes, heads): files decoded on the device"}
@@ -558,29 +608,22 @@ def run_gpu_arm(args) -> None:
             legs = [("raw_frames", h_frames, hp), ("jpeg_files", blobs, hp)]
             if B >= 128:
                 legs.append(("jpeg_files_chunk64", blobs, None))
-            for name, src, pipe in legs:
-                if pipe is None:
-                    pipe = HostPipeline(B, SRC_H, SRC_W, dev, chunk=64, slots=2, max_det=32, max_candidates=4096,
-                                        rois_per_image=8)
-                for _ in range(2):
-                    res = pipe.run(src, head, tensors_to_host=False)
-                t0.record()
-                ticket = None
-                for _ in range(e2e_steps):
-                    nxt = pipe.submit(src, head, tensors_to_host=False)
-                    if ticket is not None:
-                        res = ticket.wait()
-                    ticket = nxt
-                res = ticket.wait()
-                t1.record()
-                torch.cuda.synchronize(dev)
-                gm = t0.elapsed_time(t1)
-                assert int(res["status"].max()) == 0
-                on_gpu[name] = {"value": B * e2e_steps / (gm / 1e3), "unit": UNIT, "ms_per_step": gm / e2e_steps,
-                                "h2d_bytes_per_step": pipe.last_h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes(B)}
+            for name, src, pipe_ in legs:
+                if pipe_ is None:
+                    pipe_ = HostPipeline(B, SRC_H, SRC_W, dev, chunk=64, slots=2, max_det=32, max_candidates=4096,
+                                         rois_per_image=8)
+                gm = timed_leg(pipe_, src, head, tensors_to_host=False)
+                on_gpu[name] = {"value": world * B * e2e_steps / (gm / 1e3), "unit": UNIT, "ms_per_step": gm / e2e_steps,
+                                "h2d_bytes_per_step": pipe_.last_h2d_bytes, "d2h_bytes_per_step": pipe_.d2h_bytes(B)}
             e2e_jpeg["models_on_gpu"] = on_gpu
         except ImportError as e:
             e2e_jpeg = {"skipped": str(e)}
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     # ---------------- rank 0 only: stage lines, CPU baseline, parity spot check ----------
     del hp, h_frames, h_heads, frames, head, pipe
@@ -594,7 +637,7 @@ def run_gpu_arm(args) -> None:
         "vs_baseline": None, "dtype": "u8/f32", "data": "synthetic", "config": workload_config(B, world),
         "roofline": roofline, "kernels": kernels, "stages": stages,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, **copy_ceiling(world, e2e_value, h2d + d2h, B),
                 "api": "shared.processing.pipeline.HostPipeline.submit/wait (pinned host buffers in and out, 3 streams x 32-image chunks, 2 batches in flight)"},
         "e2e_jpeg": e2e_jpeg,
         "gpu_launches": KERNELS_PER_STEP * args.steps,
@@ -610,6 +653,19 @@ def run_gpu_arm(args) -> None:
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def copy_ceiling(world: int, e2e_value: float, bytes_per_step: int, batch: int) -> dict:
+    """How close the host-buffer leg is to what the box's pinned-memory copies alone sustain with the
+    same byte mix on `world` GPUs at once (profiles/copy_ceiling.json, scripts/copy_ceiling.py)."""
+    path = REPO / "profiles" / "copy_ceiling.json"
+    try:
+        row = json.loads(path.read_text())["by_gpus"][str(world)]
+    except Exception:
+        return {}
+    ceiling_images = row["aggregate_gbs"] * 1e9 / (bytes_per_step / batch)
+    return {"copy_ceiling_gbs": row["aggregate_gbs"], "copy_ceiling_images_per_s": ceiling_images,
+            "frac_of_copy_ceiling": e2e_value / ceiling_images}
 
 
 def cpu_baseline_leg() -> dict:

@@ -189,7 +189,23 @@ class HostTicket:
                 ev.record(self._owner.streams[slot])
                 ev.synchronize()
             self.done = True
+            # Where image i's crops are: crops[crop_start[i] : crop_start[i] + crop_count[i]].  (The
+            # crops of a chunk are packed, chunks start at multiples of chunk * rois_per_image:
+            # callers index through these two vectors instead of re-deriving that.)
+            v, o = self._views, self._owner
+            n = v["count"].shape[0]
+            offs = v["roi_offsets"].numpy()
+            idx = np.arange(n)
+            ci, li = idx // o.chunk, idx % o.chunk
+            v["crop_start"] = ci * (o.chunk * o.rpi) + offs[ci, li]
+            v["crop_count"] = offs[ci, li + 1] - offs[ci, li]
         return self._views
+
+    def crops_of(self, i: int) -> torch.Tensor:
+        """float32 [k_i, 3, S, S]: the model inputs of image i's detections (host tensor view)."""
+        v = self.wait()
+        lo = int(v["crop_start"][i])
+        return v["crops"][lo : lo + int(v["crop_count"][i])]
 
 
 class HostPipeline:
@@ -270,7 +286,8 @@ class HostPipeline:
         device — only detections, counts and ROI offsets are copied back."""
         jpeg = isinstance(frames, (list, tuple))
         n = len(frames) if jpeg else frames.shape[0]
-        assert n <= self.max_batch
+        if n > self.max_batch:
+            raise ValueError(f"batch of {n} images exceeds this pipeline's max_batch={self.max_batch}")
         if jpeg and self._decoders is None:
             from concurrent.futures import ThreadPoolExecutor
 
@@ -360,3 +377,79 @@ class HostPipeline:
         for t in self._tickets:
             if t is not None:
                 t.wait()
+
+
+class ShardedTicket:
+    """Handle of one batch submitted to a ShardedHostPipeline: ``wait()`` returns one result
+    dict per GPU (the HostPipeline dict of that GPU's shard) — ``bounds[g]`` is the [lo, hi)
+    slice of the batch GPU g processed."""
+
+    def __init__(self, futures, bounds) -> None:
+        self._futures, self.bounds = futures, bounds
+        self._tickets = None
+
+    def tickets(self) -> list:
+        if self._tickets is None:
+            self._tickets = [f.result() if f is not None else None for f in self._futures]
+        return self._tickets
+
+    def wait(self) -> list:
+        return [t.wait() if t is not None else None for t in self.tickets()]
+
+
+class ShardedHostPipeline:
+    """ONE host batch spread over several GPUs of the box from ONE process: images are
+    independent, so the batch is cut into contiguous shards (``sharding.shard_bounds``), each GPU
+    runs its shard through its own ``HostPipeline`` — own streams, own device buffers, own pinned
+    result buffers — driven by its own host thread, and nothing is exchanged between the GPUs: no
+    ``torch.distributed``, no NCCL, no peer access.  The inputs are read straight from the caller's
+    one (pinned) host buffer; per-GPU results stay in per-GPU pinned buffers and are returned as a
+    list (``ShardedTicket``), since gathering them would only add a host copy."""
+
+    def __init__(self, max_batch: int, src_h: int, src_w: int, devices=None, chunk: int = 32, slots: int = 3,
+                 **kw) -> None:
+        from concurrent.futures import ThreadPoolExecutor
+
+        from .sharding import shard_bounds
+        if devices is None:
+            devices = list(range(torch.cuda.device_count()))
+        self.devices = [torch.device("cuda", d) if isinstance(d, int) else torch.device(d) for d in devices]
+        if not self.devices:
+            raise ValueError("ShardedHostPipeline needs at least one CUDA device")
+        self.max_batch = max_batch
+        self._shard_bounds = shard_bounds
+        per = max(hi - lo for lo, hi in shard_bounds(max_batch, len(self.devices)))
+        self.pipes = []
+        for d in self.devices:
+            with torch.cuda.device(d):
+                self.pipes.append(HostPipeline(max(per, 1), src_h, src_w, d, chunk=min(chunk, max(per, 1)),
+                                               slots=slots, **kw))
+        # one launching thread per GPU: copies and launches of different GPUs are issued concurrently
+        self._threads = [ThreadPoolExecutor(max_workers=1) for _ in self.devices]
+
+    def _submit_one(self, g: int, frames, heads, tensors_to_host: bool):
+        with torch.cuda.device(self.devices[g]):
+            return self.pipes[g].submit(frames, heads, tensors_to_host)
+
+    def submit(self, frames, heads: torch.Tensor, tensors_to_host: bool = True) -> ShardedTicket:
+        """``frames`` uint8 [N,H,W,3] (or a list of N JPEG files) and ``heads`` float32 [N,A,85] in
+        HOST memory, N <= max_batch; they must stay untouched until the ticket has been waited on."""
+        n = len(frames) if isinstance(frames, (list, tuple)) else frames.shape[0]
+        if n > self.max_batch:
+            raise ValueError(f"batch of {n} images exceeds this pipeline's max_batch={self.max_batch}")
+        bounds = self._shard_bounds(n, len(self.devices))
+        futures = [self._threads[g].submit(self._submit_one, g, frames[lo:hi], heads[lo:hi], tensors_to_host)
+                   if hi > lo else None for g, (lo, hi) in enumerate(bounds)]
+        return ShardedTicket(futures, bounds)
+
+    def run(self, frames, heads: torch.Tensor, tensors_to_host: bool = True) -> list:
+        return self.submit(frames, heads, tensors_to_host).wait()
+
+    def drain(self) -> None:
+        for g, p in enumerate(self.pipes):
+            self._threads[g].submit(p.drain).result()
+
+    def close(self) -> None:
+        self.drain()
+        for t in self._threads:
+            t.shutdown()

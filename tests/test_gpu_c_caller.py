@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 from oracle import pipeline as O
-from oracle import synth
+from workloads import synth
 
 pytestmark = pytest.mark.gpu
 REPO = Path(__file__).resolve().parent.parent

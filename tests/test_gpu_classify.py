@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import pipeline as O
-from oracle import synth
+from workloads import synth
 
 pytestmark = pytest.mark.gpu
 

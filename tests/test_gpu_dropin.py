@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from oracle import pipeline as O
-from oracle import synth
+from workloads import synth
 
 pytestmark = pytest.mark.gpu
 
@@ -171,3 +171,44 @@ def test_scale_boxes_float64(sp):
         assert got.dtype == np.float64 and np.array_equal(got, O.scale_boxes(boxes, sc, pad, shape))
     with pytest.raises(TypeError):
         sp.scale_boxes(boxes.astype(np.int32), 1.0, (0, 0), (10, 10))
+
+
+def test_extract_crop_truncates_in_the_callers_dtype(sp):
+    """Reference mobilenet_preprocess.py:256: ``map(int, box[:4])`` on the caller's own values —
+    float64 coordinates that float32 cannot hold, integer boxes, and what int() refuses."""
+    from shared.processing.mobilenet_preprocess import extract_crop
+    img = synth.frames(1, 300, 400, seed=77)[0]
+    just_below = np.array([99.99999999, 10.0, 150.0, 60.99999999, 0.9, 0], dtype=np.float64)
+    assert np.float32(just_below[0]) == np.float32(100.0)  # float32 would round it up to 100
+    got = extract_crop(img, just_below)
+    assert got.shape == (50, 51, 3) and np.array_equal(got, img[10:60, 99:150])
+    assert np.array_equal(got, O.extract_crop(img, just_below))
+    big = np.array([16777217.0, 0.0, 16777300.0, 10.0], dtype=np.float64)  # > 2**24: outside the frame
+    assert extract_crop(img, big).shape == (1, 1, 3)
+    ints = np.array([20, 30, 120, 90], dtype=np.int64)
+    assert np.array_equal(extract_crop(img, ints), img[30:90, 20:120])
+    assert np.array_equal(extract_crop(img, [-5, -5, 1000, 1000]), img)
+    got = extract_crop(img, ints)
+    got[:] = 0
+    assert img[30:90, 20:120].any()  # a copy, not a view
+    with pytest.raises(ValueError):
+        extract_crop(img, np.array([np.nan, 0.0, 10.0, 10.0]))
+    with pytest.raises(OverflowError):
+        extract_crop(img, np.array([np.inf, 0.0, 10.0, 10.0]))
+
+
+def test_apply_nms_takes_any_integer_class_ids(sp):
+    """postprocess.py:116 groups with np.unique, so ids beyond the kernel's 10-bit key, negative
+    ids and int64 ids must behave like small ones (ascending class order, same kept boxes)."""
+    from shared.processing.postprocess import apply_nms
+    rng = np.random.default_rng(5)
+    n = 60
+    boxes = np.column_stack([rng.uniform(150, 490, n), rng.uniform(150, 490, n), rng.uniform(80, 250, n),
+                             rng.uniform(80, 250, n)]).astype(np.float32)
+    scores = rng.permutation(n).astype(np.float32) / n * 0.7 + 0.3
+    small = rng.integers(0, 4, n)
+    wild = np.array([-7, 1024, 5000, 2 ** 40], dtype=np.int64)[small]
+    keep_small = apply_nms(boxes, scores, small, 0.25, 0.45)
+    keep_wild = apply_nms(boxes, scores, wild, 0.25, 0.45)
+    assert keep_wild == keep_small == O.nms(boxes, scores, small, 0.25, 0.45)
+    assert keep_wild == O.nms(boxes, scores, wild, 0.25, 0.45)

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import pipeline as O
-from oracle import synth
+from workloads import synth
 
 pytestmark = pytest.mark.gpu
 
@@ -37,6 +37,32 @@ def test_device_pipeline(h, w):
     out = pipe.run(torch.from_numpy(frames).cuda(), torch.from_numpy(heads).cuda())
     torch.cuda.synchronize()
     _check_device(out, _oracle(frames, heads))
+
+
+def test_device_pipeline_full_c5_batch():
+    """BASELINE config C5 at the bench's own size: 256 x 1080p frames + (256, 25200, 85) heads in one
+    pass; every image's status / count / ROI offsets checked, 32 sampled images compared bit for
+    bit with the oracle (tensor, kept indices, rows, crops)."""
+    from shared.processing.pipeline import DevicePipeline
+
+    n, h, w = 256, 1080, 1920
+    heads = synth.head_v5(n, seed=71)
+    frames = synth.frames(n, h, w, seed=70)
+    pipe = DevicePipeline(n, h, w, "cuda", max_det=32, max_candidates=4096, rois_per_image=8)
+    out = pipe.run(torch.from_numpy(frames).cuda(), torch.from_numpy(heads).cuda())
+    torch.cuda.synchronize()
+    count = out.count.cpu().numpy()
+    offs = out.roi_offsets.cpu().numpy()
+    assert int(out.status.max()) == 0 and count.min() >= 1
+    assert np.array_equal(offs, np.concatenate([[0], np.cumsum(count)]))
+    rng = np.random.default_rng(9)
+    for i in sorted(rng.choice(n, size=32, replace=False).tolist()):
+        tensor, dets, keep, _, crops = O.run_image(frames[i], heads[i], 0.25, 0.45)
+        k = int(count[i])
+        assert k == len(keep) and out.keep[i, :k].cpu().tolist() == keep, i
+        assert np.array_equal(out.dets[i, :k].cpu().numpy(), dets), i
+        assert np.array_equal(out.tensor[i : i + 1].cpu().numpy(), tensor), i
+        assert np.array_equal(out.crops[offs[i] : offs[i + 1]].cpu().numpy(), crops), i
 
 
 def _check_host(res, want, chunk, rpi):
@@ -190,3 +216,60 @@ def test_pipelines_report_the_decode_status_of_each_file():
     assert np.array_equal(res["tensor"][4:5].numpy(), tensor)
     raw = host.run(torch.zeros(2, h, w, 3, dtype=torch.uint8).pin_memory(), heads[:2].pin_memory())
     assert raw["jpeg_status"] is None
+
+
+def _check_shards(shards, bounds, want, chunk):
+    for res, (lo, hi) in zip(shards, bounds):
+        if hi == lo:
+            assert res is None
+            continue
+        for li, i in enumerate(range(lo, hi)):
+            tensor, dets, keep, _, crops = want[i]
+            k = int(res["count"][li])
+            assert int(res["status"][li]) == 0 and k == len(keep)
+            assert res["keep"][li, :k].tolist() == keep
+            assert np.array_equal(res["tensor"][li : li + 1].numpy(), tensor)
+            assert np.array_equal(res["dets"][li, :k].numpy(), dets)
+            s, c = int(res["crop_start"][li]), int(res["crop_count"][li])
+            assert c == k and np.array_equal(res["crops"][s : s + c].numpy(), crops)
+
+
+@pytest.mark.parametrize("n_devices", [1, 2])
+def test_sharded_host_pipeline(n_devices):
+    """One host batch over several GPUs from one process: contiguous shards, one
+    HostPipeline and one launching thread per GPU, no collective.  Every image of every shard
+    equals the oracle; the two-GPU case needs a box with two GPUs."""
+    from shared.processing.pipeline import ShardedHostPipeline
+    if torch.cuda.device_count() < n_devices:
+        pytest.skip(f"needs {n_devices} GPUs")
+    h, w, n = 480, 640, 9
+    frames, heads = synth.frames(n, h, w, seed=66), synth.head_v5(n, seed=67)
+    want = _oracle(frames, heads)
+    sp = ShardedHostPipeline(n, h, w, devices=list(range(n_devices)), chunk=2, slots=2)
+    hf, hh = torch.from_numpy(frames).pin_memory(), torch.from_numpy(heads).pin_memory()
+    ticket = sp.submit(hf, hh)
+    assert ticket.bounds[0][0] == 0 and ticket.bounds[-1][1] == n
+    _check_shards(ticket.wait(), ticket.bounds, want, 2)
+    # a smaller batch right after (ragged shards, one GPU may get fewer images), then asynchronous reuse
+    t2 = sp.submit(hf[:5], hh[:5])
+    t3 = sp.submit(hf, hh)
+    _check_shards(t2.wait(), t2.bounds, want[:5], 2)
+    _check_shards(t3.wait(), t3.bounds, want, 2)
+    with pytest.raises(ValueError, match="max_batch"):
+        sp.submit(torch.cat([hf, hf]), torch.cat([hh, hh]))
+    sp.close()
+
+
+def test_host_pipeline_crop_index_and_batch_limit():
+    from shared.processing.pipeline import HostPipeline
+    h, w, n = 480, 640, 5
+    frames, heads = synth.frames(n, h, w, seed=68), synth.head_v5(n, seed=69)
+    want = _oracle(frames, heads)
+    hp = HostPipeline(n, h, w, "cuda", chunk=2, slots=2)
+    ticket = hp.submit(torch.from_numpy(frames).pin_memory(), torch.from_numpy(heads).pin_memory())
+    res = ticket.wait()
+    for i in range(n):
+        assert np.array_equal(ticket.crops_of(i).numpy(), want[i][4])
+        assert int(res["crop_count"][i]) == len(want[i][2])
+    with pytest.raises(ValueError, match="max_batch"):
+        hp.submit(torch.zeros((n + 1, h, w, 3), dtype=torch.uint8), torch.zeros((n + 1, 25200, 85)))

@@ -8,7 +8,7 @@ import pytest
 
 from conftest import sha, strided_sample
 from oracle import pipeline as P
-from oracle import synth
+from workloads import synth
 
 
 def test_letterbox_and_yolo_preprocess(golden):

@@ -37,7 +37,7 @@ def _worker(rank: int, world: int, port: int, total: int, out_path: str) -> None
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from oracle import pipeline as O
-    from oracle import synth
+    from workloads import synth
 
     lo, hi = my_shard(total)
     heads = synth.head_v5(total, seed=5, anchors=600, dup=8)  # same seed everywhere
@@ -53,7 +53,7 @@ def _worker(rank: int, world: int, port: int, total: int, out_path: str) -> None
 @pytest.mark.parametrize("total", [5, 8])
 def test_two_rank_gloo_shards_match_single_process(tmp_path, total):
     from oracle import pipeline as O
-    from oracle import synth
+    from workloads import synth
 
     out = str(tmp_path / "counts.npy")
     mp.spawn(_worker, args=(2, _free_port(), total, out), nprocs=2, join=True)

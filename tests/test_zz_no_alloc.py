@@ -16,7 +16,8 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import synth
+from oracle import pipeline as O
+from workloads import synth
 
 pytestmark = pytest.mark.gpu
 
@@ -77,19 +78,37 @@ def _assert_same(got, want):
         assert np.array_equal(g_dets[i, :k], w_dets[i, :k])  # bit-exact float32 rows
 
 
+def _assert_matches_oracle(got, head_np):
+    """The CPU oracle's kept indices and rows (oracle/pipeline.py::detect_v5, pinned to the
+    reference's own apply_nms by tests/test_oracle_golden.py), image by image."""
+    g_dets, g_keep, g_count, g_status = got
+    for i in range(head_np.shape[0]):
+        want_dets, want_keep = O.detect_v5(head_np[i], CONF, IOU)
+        k = int(g_count[i])
+        assert g_status[i] == 0 and k == len(want_keep)
+        assert g_keep[i, :k].tolist() == list(want_keep)
+        assert np.array_equal(g_dets[i, :k], want_dets)
+
+
 def test_two_calls_in_a_row_match_the_workspace_entry_point(native):
     # call 1: three images, ~100 candidates each; call 2: two images with MORE candidates per
     # image and different objects, so stale keys/counters from call 1 would show up at once
-    first = torch.from_numpy(synth.head_v5(3, seed=91)).cuda()
-    second = torch.from_numpy(synth.head_v5_dense(2, seed=92, candidates=600, anchors=5000)).cuda()
+    first_np = synth.head_v5(3, seed=91)
+    second_np = synth.head_v5_dense(2, seed=92, candidates=600, anchors=5000)
+    first, second = torch.from_numpy(first_np).cuda(), torch.from_numpy(second_np).cuda()
     want_first = _call_workspace(native, first, STATIC_MAX_CANDIDATES)
     want_second = _call_workspace(native, second, STATIC_MAX_CANDIDATES)
     assert want_first[2].min() >= 3 and want_second[2].min() > want_first[2].max()
 
-    _assert_same(_call_static(native, first, STATIC_MAX_CANDIDATES), want_first)
-    _assert_same(_call_static(native, second, STATIC_MAX_CANDIDATES), want_second)
+    got_first = _call_static(native, first, STATIC_MAX_CANDIDATES)
+    _assert_same(got_first, want_first)
+    got_second = _call_static(native, second, STATIC_MAX_CANDIDATES)
+    _assert_same(got_second, want_second)
     # and back again: fewer candidates than the leftovers now in the array
     _assert_same(_call_static(native, first, STATIC_MAX_CANDIDATES), want_first)
+    # not only equal to the other entry point: equal to the CPU oracle of the reference's decode + NMS
+    _assert_matches_oracle(got_first, first_np)
+    _assert_matches_oracle(got_second, second_np)
 
 
 def test_candidate_budget_overflow_is_reported_identically(native):

@@ -1,7 +1,8 @@
 import sys
 sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent.parent)); sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent.parent / "inference-arena_b200"))
 import numpy as np, torch
-from oracle import synth, pipeline as O
+from oracle import pipeline as O
+from workloads import synth
 from shared.processing import device as D
 dev = "cuda"
 # K1: copy / gather / linear / box2 / unaligned base / odd target
