@@ -637,7 +637,7 @@ def run_gpu_arm(args) -> None:
         "vs_baseline": None, "dtype": "u8/f32", "data": "synthetic", "config": workload_config(B, world),
         "roofline": roofline, "kernels": kernels, "stages": stages,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, **copy_ceiling(world, e2e_value, h2d + d2h, B),
+                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, **copy_ceiling(world, e2e_value, h2d, d2h, B),
                 "api": "shared.processing.pipeline.HostPipeline.submit/wait (pinned host buffers in and out, 3 streams x 32-image chunks, 2 batches in flight)"},
         "e2e_jpeg": e2e_jpeg,
         "gpu_launches": KERNELS_PER_STEP * args.steps,
@@ -655,17 +655,24 @@ def run_gpu_arm(args) -> None:
         dist.destroy_process_group()
 
 
-def copy_ceiling(world: int, e2e_value: float, bytes_per_step: int, batch: int) -> dict:
-    """How close the host-buffer leg is to what the box's pinned-memory copies alone sustain with the
-    same byte mix on `world` GPUs at once (profiles/copy_ceiling.json, scripts/copy_ceiling.py)."""
+def copy_ceiling(world: int, e2e_value: float, h2d_bytes: int, d2h_bytes: int, batch: int) -> dict:
+    """How close the host-buffer leg is to what the box's pinned-memory copies alone sustain on
+    `world` GPUs at once (profiles/copy_ceiling.json, measured by scripts/copy_ceiling.py with no
+    kernels): each direction's best rate divided by the bytes this leg moves per image in that
+    direction; the slower direction is the ceiling."""
     path = REPO / "profiles" / "copy_ceiling.json"
     try:
         row = json.loads(path.read_text())["by_gpus"][str(world)]
+        up = row["h2d_alone_gbs"] * 1e9 / (h2d_bytes / batch)
+        down = row["d2h_alone_gbs"] * 1e9 / (d2h_bytes / batch)
+        mix = row["e2e_mix_images_per_s"]
     except Exception:
         return {}
-    ceiling_images = row["aggregate_gbs"] * 1e9 / (bytes_per_step / batch)
-    return {"copy_ceiling_gbs": row["aggregate_gbs"], "copy_ceiling_images_per_s": ceiling_images,
-            "frac_of_copy_ceiling": e2e_value / ceiling_images}
+    # two yardsticks: the same copies with no kernels in between (what this software structure can
+    # reach on this host), and each direction's best rate measured alone (an upper bound that the
+    # host does not sustain when both directions run)
+    return {"copy_ceiling_images_per_s": mix, "frac_of_copy_ceiling": e2e_value / mix,
+            "copy_upper_bound_images_per_s": min(up, down), "frac_of_copy_upper_bound": e2e_value / min(up, down)}
 
 
 def cpu_baseline_leg() -> dict:

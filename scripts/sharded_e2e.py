@@ -12,7 +12,7 @@ import torch
 from shared.processing.pipeline import ShardedHostPipeline
 
 have = torch.cuda.device_count()
-per_gpu, steps = 256, 6
+per_gpu, steps = 256, 4
 res = {}
 frames = torch.randint(0, 256, (per_gpu * have, 1080, 1920, 3), dtype=torch.uint8).pin_memory()
 heads = (torch.rand((per_gpu * have, 25200, 85)) * 0.04).pin_memory()
