@@ -311,6 +311,8 @@ static int parse(const uint8_t* d, size_t n, ia_jpeg_job* job) {
   job->num_segments = job->restart_interval
                           ? (int32_t)((mcus + job->restart_interval - 1) / job->restart_interval)
                           : 1;
+  // bit positions inside the entropy-coded data are 32-bit on the device: 2^29 bytes = 2^32 bits
+  IA_RETURN_IF(n - job->scan_offset >= (1ull << 29), IA_ERR_UNSUPPORTED);
   job->file_bytes = (uint32_t)n;
   const bool swap = job->orientation >= 5;
   job->out_width = swap ? job->height : job->width;
@@ -480,7 +482,7 @@ extern "C" int ia_jpeg_decode(const ia_jpeg_job* jobs_host, const ia_jpeg_job* j
     huffman_kernel<kHuffThreads, 4, kSubseqBytes><<<grid, threads, 0, stream>>>(jobs_dev, (int)chunks, ticket, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
-  idct_kernel<<<dim3((max_blocks + kIdctThreads - 1) / kIdctThreads, n), kIdctThreads, 0, stream>>>(jobs_dev);
+  idct_kernel<<<dim3((max_blocks + kIdctThreads - 1) / kIdctThreads, n), kIdctThreads, 0, stream>>>(jobs_dev, status_dev);
   rc = launch_status();
   if (rc != IA_OK) return rc;
   const int px_per_cta = 32 * kColourPixels;

@@ -992,29 +992,36 @@ constexpr int kIdctThreads = 128;
 // 16 bits with saturation.  Inputs hold 16-bit values.
 __device__ __forceinline__ int wrap16(int x) { return (int)(int16_t)(uint16_t)(uint32_t)x; }
 
+// `left16` collects (as non-zero bits) every place where a 16-bit lane wrapped or a result was
+// saturated: while it stays 0 the SIMD evaluation is plain jidctint.c integer arithmetic.
 template <int kShift>
-__device__ __forceinline__ void idct8(const int d[8], int o[8]) {
+__device__ __forceinline__ void idct8(const int d[8], int o[8], uint32_t& left16) {
   typedef uint32_t u;
   const u tmp3 = (u)(d[2] * (4433 + 6270)) + (u)(d[6] * 4433);
   const u tmp2 = (u)(d[2] * 4433) + (u)(d[6] * (4433 - 15137));
-  const u tmp0 = (u)(wrap16(d[0] + d[4]) * 8192), tmp1 = (u)(wrap16(d[0] - d[4]) * 8192);
+  const int s04 = d[0] + d[4], d04 = d[0] - d[4], s73 = d[7] + d[3], s51 = d[5] + d[1];
+  const u tmp0 = (u)(wrap16(s04) * 8192), tmp1 = (u)(wrap16(d04) * 8192);
   const u tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
-  const int z3 = wrap16(d[7] + d[3]), z4 = wrap16(d[5] + d[1]);
+  const int z3 = wrap16(s73), z4 = wrap16(s51);
+  left16 |= (u)(s04 ^ wrap16(s04)) | (u)(d04 ^ wrap16(d04)) | (u)(s73 ^ z3) | (u)(s51 ^ z4);
   const u z3n = (u)(z3 * (9633 - 16069)) + (u)(z4 * 9633);
   const u z4n = (u)(z3 * 9633) + (u)(z4 * (9633 - 3196));
   const u t0 = (u)(d[7] * (2446 - 7373)) + (u)(d[1] * -7373) + z3n;
   const u t3 = (u)(d[7] * -7373) + (u)(d[1] * (12299 - 7373)) + z4n;
   const u t1 = (u)(d[5] * (16819 - 20995)) + (u)(d[3] * -20995) + z4n;
   const u t2 = (u)(d[5] * -20995) + (u)(d[3] * (25172 - 20995)) + z3n;
-  auto fin = [](u x) -> int {
+  auto fin = [&left16](u x) -> int {
     const int v = (int)(x + (1u << (kShift - 1))) >> kShift;
-    return max(-32768, min(32767, v));
+    const int c = max(-32768, min(32767, v));
+    left16 |= (u)(v ^ c);
+    return c;
   };
   o[0] = fin(tmp10 + t3), o[7] = fin(tmp10 - t3), o[1] = fin(tmp11 + t2), o[6] = fin(tmp11 - t2);
   o[2] = fin(tmp12 + t1), o[5] = fin(tmp12 - t1), o[3] = fin(tmp13 + t0), o[4] = fin(tmp13 - t0);
 }
 
-__global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* __restrict__ jobs) {
+__global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* __restrict__ jobs,
+                                                            int32_t* __restrict__ status) {
   const ia_jpeg_job& J = jobs[blockIdx.y];
   __shared__ uint16_t s_quant[IA_JPEG_MAX_COMPONENTS][64];
   for (int i = threadIdx.x; i < IA_JPEG_MAX_COMPONENTS * 64; i += kIdctThreads)
@@ -1033,7 +1040,8 @@ __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* _
   const uint4* __restrict__ src = reinterpret_cast<const uint4*>(J.coef_dev + (size_t)g * 64);
   const uint16_t* q = s_quant[c];
   int ws[64];
-  uint32_t below = 0;  // any coefficient in rows 1..7
+  uint32_t left16 = 0;  // a 16-bit lane wrapped / saturated somewhere in this block
+  uint32_t below = 0;   // any coefficient in rows 1..7
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
     const uint4 v = __ldg(src + r);
@@ -1041,8 +1049,11 @@ __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* _
     if (r) below |= v.x | v.y | v.z | v.w;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {  // dequantise in a 16-bit lane (pmullw)
-      ws[r * 8 + 2 * i] = wrap16((int)((w[i] & 0xffffu) * (uint32_t)q[r * 8 + 2 * i]));
-      ws[r * 8 + 2 * i + 1] = wrap16((int)((w[i] >> 16) * (uint32_t)q[r * 8 + 2 * i + 1]));
+      const int lo = (int)(int16_t)(w[i] & 0xffffu) * (int)q[r * 8 + 2 * i];
+      const int hi = (int)(int16_t)(w[i] >> 16) * (int)q[r * 8 + 2 * i + 1];
+      ws[r * 8 + 2 * i] = wrap16(lo);
+      ws[r * 8 + 2 * i + 1] = wrap16(hi);
+      left16 |= (uint32_t)(lo ^ wrap16(lo)) | (uint32_t)(hi ^ wrap16(hi));
     }
   }
   if (below == 0) {
@@ -1050,6 +1061,7 @@ __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* _
 #pragma unroll
     for (int col = 0; col < 8; ++col) {
       const int v = wrap16(ws[col] << 2);
+      left16 |= (uint32_t)((ws[col] << 2) ^ v);
 #pragma unroll
       for (int r = 0; r < 8; ++r) ws[r * 8 + col] = v;
     }
@@ -1060,7 +1072,7 @@ __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* _
       int d[8], o[8];
 #pragma unroll
       for (int r = 0; r < 8; ++r) d[r] = ws[r * 8 + col];
-      idct8<11>(d, o);
+      idct8<11>(d, o, left16);
 #pragma unroll
       for (int r = 0; r < 8; ++r) ws[r * 8 + col] = o[r];
     }
@@ -1071,7 +1083,7 @@ __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* _
     int d[8], o[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) d[i] = ws[r * 8 + i];
-    idct8<18>(d, o);
+    idct8<18>(d, o, left16);
     uint32_t px[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) px[i] = (uint32_t)(max(-128, min(127, o[i])) + 128);
@@ -1080,6 +1092,11 @@ __global__ void __launch_bounds__(kIdctThreads) idct_kernel(const ia_jpeg_job* _
     out.y = px[4] | (px[5] << 8) | (px[6] << 16) | (px[7] << 24);
     *reinterpret_cast<uint2*>(dst + (size_t)r * pitch) = out;
   }
+  // Coefficients no encoder produces (damaged data) pushed a 16-bit lane of the SIMD evaluation over
+  // its range.  The wrap-arounds above follow libjpeg-turbo's code, but only the in-range case is
+  // plain jidctint.c arithmetic and therefore certain to be cv2's pixels: such a frame is reported
+  // as damaged (status bit 0), never as clean.
+  if (left16) atomicOr(status + blockIdx.y, 1);
 }
 
 // ====================================================================== upsample + colour

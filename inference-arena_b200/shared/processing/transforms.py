@@ -32,12 +32,31 @@ def load_image(image_path: str) -> np.ndarray:
 
 
 def load_image_from_bytes(image_bytes: bytes) -> np.ndarray:
-    """Decode encoded image bytes to RGB uint8 [H, W, 3] (host side)."""
-    import cv2
+    """Decode encoded image bytes to RGB uint8 [H, W, 3] (reference transforms.py:77-110).
 
+    A baseline JPEG — what the services receive (monolithic/app/inference.py:153) — is decoded on
+    the GPU (``shared.processing.jpeg``, bit-identical to ``cv2.imdecode``): only the compressed
+    bytes cross PCIe.  Everything the device decoder does not take (PNG and other formats,
+    progressive / arithmetic / CMYK JPEGs) and any file it reports as damaged goes through
+    ``cv2.imdecode`` on the host exactly as in the reference, so the pixels and the two
+    ``ValueError`` messages are the reference's for every input."""
     if not image_bytes:
         raise ValueError("Failed to decode image from bytes: empty input")
-    bgr = cv2.imdecode(np.frombuffer(image_bytes, np.uint8), cv2.IMREAD_COLOR)
+    data = bytes(image_bytes)
+    if data[:2] == b"\xff\xd8":
+        from shared.processing import jpeg as _jpeg
+        try:
+            batch = _jpeg.decode_jpeg_batch_cuda([data])
+            status = int(batch.status[0])  # synchronises
+            if status == 0:
+                return batch.frames[0].cpu().numpy()
+            if status & 2:  # the data ends before the last block: cv2.imdecode returns None here
+                raise ValueError("Failed to decode image from bytes")
+        except _jpeg.UnsupportedJpeg:
+            pass
+    import cv2
+
+    bgr = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)
     if bgr is None:
         raise ValueError("Failed to decode image from bytes")
     return cv2.cvtColor(bgr, cv2.COLOR_BGR2RGB)

@@ -523,6 +523,55 @@ def _idct_1d(d0, d1, d2, d3, d4, d5, d6, d7, shift):
     return [_sat16(_w32(_w32(o) + (1 << (shift - 1))) >> shift) for o in outs]
 
 
+def idct_left_16bit_range(coef: np.ndarray, quant: np.ndarray) -> np.ndarray:
+    """bool [...]: True for a block in which a 16-bit lane of the SIMD evaluation wraps or a
+    descaled result saturates (dequantised coefficient, the sums in0 +- in4 / in7 + in3 / in5 +
+    in1 of either pass, the packed results of either pass).  While it is False the SIMD code is
+    plain jidctint.c integer arithmetic — the only case in which the pixels are certain to be
+    cv2's; the device reports frames containing such a block as damaged (status bit 0)."""
+    c = coef.astype(np.int64)
+    dq = c * quant.astype(np.int64)
+    bad = np.any(dq != _w16(dq), axis=-1)
+    d = _w16(dq).reshape(c.shape[:-1] + (8, 8))
+
+    def lanes(rows):  # rows: list of 8 arrays (the 8 inputs of a 1-D pass)
+        d0, d1, d2, d3, d4, d5, d6, d7 = rows
+        out = np.zeros(d0.shape, dtype=bool)
+        for v in (d0 + d4, d0 - d4, d7 + d3, d5 + d1):
+            out |= v != _w16(v)
+        return out
+
+    def unsat(rows, shift):
+        d0, d1, d2, d3, d4, d5, d6, d7 = rows
+        tmp3 = d2 * (4433 + 6270) + d6 * 4433
+        tmp2 = d2 * 4433 + d6 * (4433 - 15137)
+        tmp0, tmp1 = _w16(d0 + d4) << 13, _w16(d0 - d4) << 13
+        z3, z4 = _w16(d7 + d3), _w16(d5 + d1)
+        z3, z4 = z3 * (9633 - 16069) + z4 * 9633, z3 * 9633 + z4 * (9633 - 3196)
+        t0 = d7 * (2446 - 7373) + d1 * -7373 + z3
+        t3 = d7 * -7373 + d1 * (12299 - 7373) + z4
+        t1 = d5 * (16819 - 20995) + d3 * -20995 + z4
+        t2 = d5 * -20995 + d3 * (25172 - 20995) + z3
+        outs = (tmp0 + tmp3 + t3, tmp1 + tmp2 + t2, tmp1 - tmp2 + t1, tmp0 - tmp3 + t0,
+                tmp0 - tmp3 - t0, tmp1 - tmp2 - t1, tmp1 + tmp2 - t2, tmp0 + tmp3 - t3)
+        res = np.zeros(d0.shape, dtype=bool)
+        for o in outs:
+            v = (_w32(o) + (1 << (shift - 1))) >> shift
+            res |= v != _sat16(v)
+        return res
+
+    flat = ~np.any(c[..., 8:] != 0, axis=-1)
+    rows1 = [d[..., r, :] for r in range(8)]
+    pass1 = np.any(lanes(rows1) | unsat(rows1, 11), axis=-1)
+    short = np.any((d[..., 0, :] << 2) != _w16(d[..., 0, :] << 2), axis=-1)
+    bad |= np.where(flat, short, pass1)
+    ws = np.stack(_idct_1d(*rows1, shift=11), axis=-2)
+    ws = np.where(flat[..., None, None], _w16(d[..., :1, :] << 2), ws)
+    rows2 = [ws[..., :, k] for k in range(8)]
+    bad |= np.any(lanes(rows2) | unsat(rows2, 18), axis=-1)
+    return bad
+
+
 def idct_islow(coef: np.ndarray, quant: np.ndarray) -> np.ndarray:
     """coef [..., 64] natural order (int16 values), quant [64] -> uint8 [..., 8, 8] (jidctint.c
     jpeg_idct_islow: columns first with DESCALE by 11, then rows with DESCALE by 18, the

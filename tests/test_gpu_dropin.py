@@ -212,3 +212,40 @@ def test_apply_nms_takes_any_integer_class_ids(sp):
     keep_wild = apply_nms(boxes, scores, wild, 0.25, 0.45)
     assert keep_wild == keep_small == O.nms(boxes, scores, small, 0.25, 0.45)
     assert keep_wild == O.nms(boxes, scores, wild, 0.25, 0.45)
+
+
+def test_load_image_from_bytes_uses_the_device_decoder_and_keeps_cv2_pixels(sp, golden, monkeypatch):
+    """The drop-in name the services call (reference transforms.py:77-110): baseline JPEGs take the
+    GPU decoder, everything else cv2 on the host; pixels and error messages are the reference's."""
+    cv2 = pytest.importorskip("cv2")
+    from shared.processing import jpeg as jpeg_mod
+    from shared.processing.transforms import load_image_from_bytes
+
+    calls = []
+    real = jpeg_mod.decode_jpeg_batch_cuda
+    monkeypatch.setattr(jpeg_mod, "decode_jpeg_batch_cuda", lambda blobs, *a, **k: (calls.append(len(blobs)), real(blobs, *a, **k))[1])
+
+    def cv2_rgb(data):
+        return cv2.cvtColor(cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR), cv2.COLOR_BGR2RGB)
+
+    for i in range(8):  # files the unmodified reference decoded when the golden vectors were made
+        data = golden[f"jpeg{i}_bytes"].tobytes()
+        got = load_image_from_bytes(data)
+        assert got.dtype == np.uint8 and got.flags["C_CONTIGUOUS"]
+        assert np.array_equal(got, golden[f"jpeg{i}_rgb"]) and np.array_equal(got, cv2_rgb(data))
+    assert len(calls) == 8  # all eight went through the device
+    img = synth.frames(1, 48, 64, seed=5)[0]
+    smooth = (img // 8 + np.arange(64, dtype=np.uint8)[None, :, None] * 2).astype(np.uint8)
+    png = cv2.imencode(".png", cv2.cvtColor(smooth, cv2.COLOR_RGB2BGR))[1].tobytes()
+    assert np.array_equal(load_image_from_bytes(png), smooth) and len(calls) == 8  # not a JPEG: host only
+    prog = cv2.imencode(".jpg", smooth, [cv2.IMWRITE_JPEG_QUALITY, 90, cv2.IMWRITE_JPEG_PROGRESSIVE, 1])[1].tobytes()
+    assert np.array_equal(load_image_from_bytes(prog), cv2_rgb(prog))  # refused by the device, decoded by cv2
+    damaged = (__import__("pathlib").Path(__file__).parent / "golden" / "jpeg_idct_overflow_case.jpg").read_bytes()
+    assert np.array_equal(load_image_from_bytes(damaged), cv2_rgb(damaged))  # flagged by the device -> cv2's pixels
+    assert np.array_equal(load_image_from_bytes(bytearray(golden["jpeg0_bytes"].tobytes())), golden["jpeg0_rgb"])
+    with pytest.raises(ValueError, match="empty input"):
+        load_image_from_bytes(b"")
+    with pytest.raises(ValueError, match="Failed to decode"):
+        load_image_from_bytes(b"not an image at all")
+    with pytest.raises(ValueError, match="Failed to decode"):
+        load_image_from_bytes(golden["jpeg0_bytes"].tobytes()[:200])  # a JPEG cut inside its headers

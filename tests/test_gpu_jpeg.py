@@ -399,8 +399,9 @@ def test_motion_jpeg_frames_without_huffman_tables(M):
 def test_out_of_range_coefficients_wrap_like_the_simd_idct(M):
     """Quantisation tables far beyond what the coefficients were coded for: the dequantised values
     leave 16 bits, and what comes out is defined by libjpeg-turbo's SIMD IDCT (16-bit lanes that
-    wrap, saturating packs), which is what OpenCV runs.  The entropy decode is untouched, so
-    every file must come back with status 0 and cv2's pixels."""
+    wrap, saturating packs), which is what OpenCV runs.  Every file must come back with cv2's
+    pixels, and — the entropy decode being untouched — flagged (status 1) exactly when the oracle's
+    twin of the range check finds a block that left the 16-bit range."""
     rng = np.random.default_rng(5)
     blobs = []
     for i, sampling in enumerate(("420", "444", "422", "411")):
@@ -423,7 +424,12 @@ def test_out_of_range_coefficients_wrap_like_the_simd_idct(M):
     wants = [W.reference_decode(b) for b in blobs]
     batch = M.decode_jpeg_batch_cuda(blobs)
     torch.cuda.synchronize()
-    assert batch.status.cpu().tolist() == [0] * len(blobs)
+    expect = []
+    for b in blobs:
+        info = J.parse(b)
+        expect.append(int(any(J.idct_left_16bit_range(cf, info["qt"][c["tq"]]).any()
+                              for c, cf in zip(info["comps"], J.decode_coefficients(b, info)))))
+    assert batch.status.cpu().tolist() == expect and sum(expect) >= 8
     for got, want in zip(batch.frames, wants):
         assert np.array_equal(got.cpu().numpy(), want)
     assert len(blobs) == 16
@@ -495,3 +501,27 @@ def test_two_decoders_on_two_streams(M):
     for o1, o2 in outs[:-1]:  # frames of earlier calls are the callers' own tensors: still intact
         assert np.array_equal(o1.frames[0].cpu().numpy(), W.reference_decode(a[0]))
         assert np.array_equal(o2.frames[5].cpu().numpy(), W.reference_decode(b[5]))
+
+
+def test_out_of_range_idct_block_is_flagged_not_clean(M):
+    """tests/golden/jpeg_idct_overflow_case.jpg: a damaged file whose luma block (23, 55) drives the
+    16-bit lanes of libjpeg-turbo's SIMD IDCT over their range; cv2 decodes it (8 pixels of that
+    block differ from the modelled wrap-arounds).  Such a frame must not come back as clean:
+    status bit 0 is set, the oracle's twin of the check names exactly that block, and every
+    other pixel is cv2's."""
+    import cv2
+    from pathlib import Path
+    data = (Path(__file__).parent / "golden" / "jpeg_idct_overflow_case.jpg").read_bytes()
+    want = cv2.cvtColor(cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR), cv2.COLOR_BGR2RGB)
+    info = J.parse(data)
+    coefs = J.decode_coefficients(data, info)
+    flagged = [np.argwhere(J.idct_left_16bit_range(cf, info["qt"][c["tq"]])).tolist()
+               for c, cf in zip(info["comps"], coefs)]
+    assert flagged == [[[23, 55]], [], []]
+    clean = W.encode(W.photo(600, 800, seed=3), 90, "420")
+    batch = M.decode_jpeg_batch_cuda([clean, data, clean])
+    torch.cuda.synchronize()
+    assert batch.status.cpu().tolist() == [0, 1, 0]  # flagged as damaged; the neighbours in the batch are not
+    got = batch.frames[1].cpu().numpy()
+    differs = np.argwhere((got != want).any(axis=-1))
+    assert len(differs) == 0 or (differs.min(0) >= [23 * 8 - 1, 55 * 8 - 1]).all() and (differs.max(0) <= [23 * 8 + 8, 55 * 8 + 8]).all()

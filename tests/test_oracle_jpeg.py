@@ -341,3 +341,24 @@ def test_no_cpu_fallback(jpeg_mod):
         pytest.skip("CUDA present")
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         jpeg_mod.decode_jpeg_batch_cuda([W.encode(W.photo(16, 16, 1), 90)])
+
+
+def test_idct_range_check_flags_only_the_damaged_block():
+    """oracle.jpeg.idct_left_16bit_range: no block of a valid encoding leaves the 16-bit range of the
+    SIMD IDCT (there the SIMD code is plain jidctint.c arithmetic), the committed damaged file has
+    exactly one that does."""
+    from pathlib import Path
+    import cv2
+    rng = np.random.default_rng(0)
+    noise = rng.integers(0, 256, (96, 128, 3), dtype=np.uint8)
+    blobs = [W.encode(W.photo(120, 160, seed=q), q, s) for q in (5, 60, 100) for s in ("444", "420")]
+    blobs += [cv2.imencode(".jpg", noise, [cv2.IMWRITE_JPEG_QUALITY, q])[1].tobytes() for q in (1, 100)]
+    for blob in blobs:
+        info = J.parse(blob)
+        for c, cf in zip(info["comps"], J.decode_coefficients(blob, info)):
+            assert not J.idct_left_16bit_range(cf, info["qt"][c["tq"]]).any()
+    data = (Path(__file__).parent / "golden" / "jpeg_idct_overflow_case.jpg").read_bytes()
+    info = J.parse(data)
+    hits = [int(J.idct_left_16bit_range(cf, info["qt"][c["tq"]]).sum())
+            for c, cf in zip(info["comps"], J.decode_coefficients(data, info))]
+    assert hits == [1, 0, 0]
