@@ -218,14 +218,22 @@ int ia_imagenet_normalize_u8(const uint8_t* image_dev, size_t pixels, const floa
  * src/shared/processing/mobilenet_preprocess.py:114-160 with :204-206 (float32 accepted) and
  * imagenet_normalize's float branch, transforms.py:264-267 (divide by 255 only when the
  * maximum exceeds 1).  crop_dev float [h, w, 3] -> out_chw_dev float [3, out_size, out_size].
- * The resize is OpenCV's generic float INTER_LINEAR (bit-identical to cv2.resize with IPP
- * off; pip builds of OpenCV use Intel IPP for float resizes, which differs by up to ~3e-5).
+ * cv2.resize on float data depends on the OpenCV build, so the resize comes in two flavours, each
+ * bit-identical to its build: IA_F32_RESIZE_IPP — the opencv-python wheels the reference pins
+ * (uv.lock:2549-2550) hand float resizes to Intel IPP; IA_F32_RESIZE_OPENCV — OpenCV's own
+ * generic float INTER_LINEAR, what cv2 computes with IPP off or absent.  (On [0,1] data the two
+ * differ by up to ~3e-5.)  ia_resize_normalize_f32 is the OPENCV flavour.
  * scratch_dev: 16-byte aligned, at least ia_f32_scratch_bytes(out_size) bytes.
  * ------------------------------------------------------------------------------- */
+#define IA_F32_RESIZE_OPENCV 0
+#define IA_F32_RESIZE_IPP 1
 size_t ia_f32_scratch_bytes(int out_size);
 int ia_resize_normalize_f32(const float* crop_dev, int h, int w, int out_size, const float mean[3],
                             const float std[3], float* out_chw_dev, void* scratch_dev,
                             size_t scratch_bytes, void* stream);
+int ia_resize_normalize_f32_as(const float* crop_dev, int h, int w, int out_size, int flavour,
+                               const float mean[3], const float std[3], float* out_chw_dev,
+                               void* scratch_dev, size_t scratch_bytes, void* stream);
 
 /* imagenet_normalize() on float32 HWC, transforms.py:264-270 -> float HWC.  scratch_dev: 8 bytes. */
 int ia_imagenet_normalize_f32(const float* image_dev, size_t pixels, const float mean[3],

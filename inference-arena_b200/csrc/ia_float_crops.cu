@@ -3,11 +3,16 @@
 // transforms.py:264-267 rescales them by 1/255 only when their maximum exceeds 1).
 //
 // Not a throughput path (the reference's pipelines only ever pass uint8 crops); it exists so
-// the drop-in covers the whole signature on the GPU.  The resize follows OpenCV's generic
-// float INTER_LINEAR (resize.cpp HResizeLinear<float>/VResizeLinear<float>: float
-// coefficients 1-f and f, every product and sum rounded separately) and is bit-identical to
-// cv2.resize with IPP disabled; pip builds of OpenCV route float resizes through Intel IPP,
-// whose unpublished arithmetic differs by up to ~3e-5 (see tests/test_oracle_cv_resize.py).
+// the drop-in covers the whole signature on the GPU.  Two flavours of the float resize, both
+// bit-identical to what cv2.resize returns in the corresponding build (oracle/cv_resize.py,
+// tests/test_oracle_cv_resize.py):
+//   IA_F32_RESIZE_IPP     the opencv-python wheels the reference pins: float resizes go to Intel
+//                         IPP — double coordinates, weight = float(pos - floor(pos)), every
+//                         interpolation fma(p1 - p0, w, p0), horizontal then vertical, no box
+//                         average for exact 2x; one-pixel-wide/high images take the generic path;
+//   IA_F32_RESIZE_OPENCV  OpenCV's own generic float INTER_LINEAR (resize.cpp HResizeLinear<float>
+//                         / VResizeLinear<float>: float coefficients 1-f and f, every product
+//                         and sum rounded separately; exact 2x = box average): cv2 with IPP off.
 #include "ia_common.cuh"
 
 namespace ia {
@@ -34,6 +39,22 @@ __device__ __forceinline__ FloatAxis axis_coef_f32(int i, double sc, int src, bo
   return a;
 }
 
+// IPP: tap and weight from the double coordinate (the fraction is not rounded to float first).
+struct IppAxis {
+  int s0, s1;
+  float w;
+};
+__device__ __forceinline__ IppAxis axis_coef_ipp(int i, double sc, int src) {
+  const double pos = __dsub_rn(__dmul_rn(__dadd_rn((double)i, 0.5), sc), 0.5);
+  const double fl = floor(pos);
+  IppAxis a;
+  a.w = __double2float_rn(__dsub_rn(pos, fl));
+  const int s0 = __double2int_rd(fl);
+  a.s0 = clampi(s0, 0, src - 1);
+  a.s1 = clampi(s0 + 1, 0, src - 1);
+  return a;
+}
+
 __device__ __forceinline__ uint32_t ordered_bits(float f) {
   const uint32_t u = __float_as_uint(f);
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
@@ -52,6 +73,8 @@ __device__ __forceinline__ void publish_max(float v, bool nan, uint32_t* stats) 
 }
 
 // One thread per output pixel (3 channels): src float [h,w,3] -> dst float [S,S,3] (HWC).
+constexpr int kResizeIpp = 100;  // mode value: IPP's bilinear (see the file header)
+
 __global__ void resize_f32_kernel(const float* __restrict__ src, int h, int w, int S, double sc_x,
                                   double sc_y, int mode, float* __restrict__ dst, uint32_t* stats) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -62,6 +85,17 @@ __global__ void resize_f32_kernel(const float* __restrict__ src, int h, int w, i
     if (mode == kResizeCopy) {
       const float* p = src + ((size_t)y * w + x) * 3;
       out[0] = p[0], out[1] = p[1], out[2] = p[2];
+    } else if (mode == kResizeIpp) {
+      const IppAxis ax = axis_coef_ipp(x, sc_x, w), ay = axis_coef_ipp(y, sc_y, h);
+      const float* p0 = src + (size_t)ay.s0 * w * 3;
+      const float* p1 = src + (size_t)ay.s1 * w * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float a0 = p0[ax.s0 * 3 + c], a1 = p1[ax.s0 * 3 + c];
+        const float h0 = __fmaf_rn(__fsub_rn(p0[ax.s1 * 3 + c], a0), ax.w, a0);
+        const float h1 = __fmaf_rn(__fsub_rn(p1[ax.s1 * 3 + c], a1), ax.w, a1);
+        out[c] = __fmaf_rn(__fsub_rn(h1, h0), ay.w, h0);
+      }
     } else if (mode == kResizeBox2) {  // ResizeAreaFast: ((p00 + p01) + p10) + p11, times 0.25
       const float* a = src + ((size_t)(2 * y) * w + 2 * x) * 3;
       const float* b = a + (size_t)w * 3;
@@ -132,8 +166,16 @@ extern "C" size_t ia_f32_scratch_bytes(int out_size) {
 
 extern "C" int ia_resize_normalize_f32(const float* crop_dev, int h, int w, int out_size,
                                        const float mean[3], const float std[3], float* out_chw_dev,
-                                       void* scratch_dev, size_t scratch_bytes, void* stream_) {
+                                       void* scratch_dev, size_t scratch_bytes, void* stream) {
+  return ia_resize_normalize_f32_as(crop_dev, h, w, out_size, IA_F32_RESIZE_OPENCV, mean, std, out_chw_dev,
+                                    scratch_dev, scratch_bytes, stream);
+}
+
+extern "C" int ia_resize_normalize_f32_as(const float* crop_dev, int h, int w, int out_size, int flavour,
+                                          const float mean[3], const float std[3], float* out_chw_dev,
+                                          void* scratch_dev, size_t scratch_bytes, void* stream_) {
   using namespace ia;
+  IA_RETURN_IF(flavour != IA_F32_RESIZE_OPENCV && flavour != IA_F32_RESIZE_IPP, IA_ERR_INVALID_ARGUMENT);
   cudaStream_t stream = (cudaStream_t)stream_;
   IA_RETURN_IF(!crop_dev || !mean || !std || !out_chw_dev || !scratch_dev, IA_ERR_INVALID_ARGUMENT);
   IA_RETURN_IF(h < 1 || w < 1 || out_size < 1 || ((uintptr_t)scratch_dev & 15) != 0, IA_ERR_INVALID_ARGUMENT);
@@ -143,9 +185,15 @@ extern "C" int ia_resize_normalize_f32(const float* crop_dev, int h, int w, int 
   cudaError_t e = cudaMemsetAsync(stats, 0, 8, stream);
   if (e != cudaSuccess) return (int)e;
   const int pixels = out_size * out_size;
-  resize_f32_kernel<<<(pixels + 255) / 256, 256, 0, stream>>>(crop_dev, h, w, out_size, axis_scale(out_size, w),
-                                                              axis_scale(out_size, h),
-                                                              resize_mode(h, w, out_size, out_size), resized, stats);
+  int mode = resize_mode(h, w, out_size, out_size);
+  double sc_x = axis_scale(out_size, w), sc_y = axis_scale(out_size, h);
+  if (flavour == IA_F32_RESIZE_IPP && mode != kResizeCopy && h >= 2 && w >= 2) {
+    mode = kResizeIpp;
+    sc_x = (double)w / (double)out_size;
+    sc_y = (double)h / (double)out_size;
+  }
+  resize_f32_kernel<<<(pixels + 255) / 256, 256, 0, stream>>>(crop_dev, h, w, out_size, sc_x, sc_y, mode, resized,
+                                                              stats);
   int rc = launch_status();
   if (rc != IA_OK) return rc;
   normalize_f32_kernel<<<grid_for(pixels, 256), 256, 0, stream>>>(resized, (size_t)pixels, stats, mean[0], mean[1],

@@ -16,6 +16,8 @@ LIB_PATH = Path(os.environ.get("IA_B200_LIB", PACKAGE_ROOT / "lib" / "libia_b200
 
 IA_HEAD_LAYOUT_V5 = 0
 IA_HEAD_LAYOUT_V8 = 1
+IA_F32_RESIZE_OPENCV = 0
+IA_F32_RESIZE_IPP = 1
 
 
 class LetterboxGeom(ctypes.Structure):
@@ -62,6 +64,8 @@ _SIGNATURES = {
                                          F3, c_void_p, c_void_p]),
     "ia_extract_crop_rects": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ia_f32_scratch_bytes": (c_size_t, [c_int]),
+    "ia_resize_normalize_f32_as": (c_int, [c_void_p, c_int, c_int, c_int, c_int, F3, F3, c_void_p, c_void_p, c_size_t,
+                                           c_void_p]),
     "ia_resize_normalize_f32": (c_int, [c_void_p, c_int, c_int, c_int, F3, F3, c_void_p, c_void_p, c_size_t,
                                         c_void_p]),
     "ia_imagenet_normalize_f32": (c_int, [c_void_p, c_size_t, F3, F3, c_void_p, c_void_p, c_size_t, c_void_p]),

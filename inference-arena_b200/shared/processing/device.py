@@ -321,10 +321,25 @@ def crop_ragged_cuda(frames: list[torch.Tensor], dets: torch.Tensor, count: torc
 
 
 # --------------------------------------------------------------- float32-input branch (N2)
+def float_resize_flavour() -> str:
+    """Which cv2 build the float32-crop resize reproduces bit for bit: ``"ipp"`` (default — the
+    opencv-python wheels the reference pins route float resizes through Intel IPP) or ``"opencv"``
+    (OpenCV's own generic path: cv2 built without IPP or with ``cv2.ipp.setUseIPP(False)``).
+    Chosen with the environment variable ``IA_F32_RESIZE``."""
+    import os
+    flavour = os.environ.get("IA_F32_RESIZE", "ipp").lower()
+    if flavour not in ("ipp", "opencv"):
+        raise ValueError(f"IA_F32_RESIZE must be 'ipp' or 'opencv', got {flavour!r}")
+    return flavour
+
+
 def resize_normalize_f32_cuda(crop: torch.Tensor, out_size: int = 224, mean=(0.485, 0.456, 0.406),
-                              std=(0.229, 0.224, 0.225)) -> torch.Tensor:
+                              std=(0.229, 0.224, 0.225), flavour: str | None = None) -> torch.Tensor:
     """MobileNetPreprocessor.preprocess on a float32 [H,W,3] CUDA crop (reference
-    mobilenet_preprocess.py:114-160, float branch) -> float32 [1,3,S,S]."""
+    mobilenet_preprocess.py:114-160, float branch) -> float32 [1,3,S,S].  ``flavour``: see
+    :func:`float_resize_flavour`."""
+    flavour = flavour or float_resize_flavour()
+    code = _native.IA_F32_RESIZE_IPP if flavour == "ipp" else _native.IA_F32_RESIZE_OPENCV
     crop = _require_cuda(crop, torch.float32, "crop")
     h, w, _ = crop.shape
     dev = crop.device
@@ -332,10 +347,11 @@ def resize_normalize_f32_cuda(crop: torch.Tensor, out_size: int = 224, mean=(0.4
     need = lib().ia_f32_scratch_bytes(int(out_size))
     scratch = torch.empty(need, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib().ia_resize_normalize_f32(crop.data_ptr(), h, w, int(out_size),
-                                            F3(*[float(np.float32(v)) for v in mean]),
-                                            F3(*[float(np.float32(v)) for v in std]), out.data_ptr(),
-                                            scratch.data_ptr(), need, _stream_ptr(dev)), "ia_resize_normalize_f32")
+        check(lib().ia_resize_normalize_f32_as(crop.data_ptr(), h, w, int(out_size), code,
+                                               F3(*[float(np.float32(v)) for v in mean]),
+                                               F3(*[float(np.float32(v)) for v in std]), out.data_ptr(),
+                                               scratch.data_ptr(), need, _stream_ptr(dev)),
+              "ia_resize_normalize_f32_as")
     return out
 
 

@@ -141,3 +141,45 @@ def resize_linear_f32(img: np.ndarray, dst_w: int, dst_h: int) -> np.ndarray:
     h = (img[:, x0] * a0[None, :, None]).astype(np.float32) + (img[:, x1] * a1[None, :, None]).astype(np.float32)
     out = (h[r0] * b0[:, None, None]).astype(np.float32) + (h[r1] * b1[:, None, None]).astype(np.float32)
     return out.astype(np.float32)
+
+
+def resize_linear_f32_ipp(img: np.ndarray, dst_w: int, dst_h: int) -> np.ndarray:
+    """``cv2.resize(img, (dst_w, dst_h), INTER_LINEAR)`` for float32 HWC as the opencv-python
+    WHEELS compute it (the reference pins opencv-python 4.11.0.86, ``uv.lock:2549-2550``): those
+    builds hand float resizes to Intel IPP (``ipp_resize`` in resize.cpp, ``ippiResizeLinear_32f``).
+    IPP's arithmetic is not published; the following was found by differential testing against
+    cv2 4.13.0 (IPP 2022.2) and is bit-identical to it on every shape tried
+    (tests/test_oracle_cv_resize.py):
+
+    * coordinates in double, ``pos = (i + 0.5) * (src / dst) - 0.5``; the tap is ``floor(pos)``
+      and the weight ``float32(pos - floor(pos))`` — the fraction is NOT rounded to float32
+      before the floor is subtracted (OpenCV's own tables do that);
+    * both taps clamped to the image (replicated border);
+    * each interpolation is ``fma(p1 - p0, w, p0)`` (difference rounded to float32, then one
+      fused multiply-add), horizontal pass first, then vertical;
+    * an exact 2x downscale is interpolated like any other size (no box average);
+    * equal sizes are a copy; an image with a side of one pixel is refused by IPP and takes
+      OpenCV's generic path (``resize_linear_f32``)."""
+    assert img.dtype == np.float32 and img.ndim == 3
+    src_h, src_w = img.shape[:2]
+    if (dst_h, dst_w) == (src_h, src_w):
+        return img.copy()
+    if src_h < 2 or src_w < 2:
+        return resize_linear_f32(img, dst_w, dst_h)
+
+    def fma(a, b, c):  # exact: the product of two float32 is exact in float64
+        return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(np.float32)
+
+    def table(dst, src):
+        pos = (np.arange(dst, dtype=np.float64) + 0.5) * (float(src) / float(dst)) - 0.5
+        s0 = np.floor(pos)
+        w = (pos - s0).astype(np.float32)
+        s0 = s0.astype(np.int64)
+        return np.clip(s0, 0, src - 1), np.clip(s0 + 1, 0, src - 1), w
+
+    x0, x1, wx = table(dst_w, src_w)
+    y0, y1, wy = table(dst_h, src_h)
+    p0, p1 = img[:, x0], img[:, x1]
+    h = fma((p1 - p0).astype(np.float32), np.broadcast_to(wx[None, :, None], p0.shape), p0)
+    q0, q1 = h[y0], h[y1]
+    return fma((q1 - q0).astype(np.float32), np.broadcast_to(wy[:, None, None], q0.shape), q0)

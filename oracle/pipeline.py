@@ -16,7 +16,7 @@ from dataclasses import dataclass
 
 import numpy as np
 
-from .cv_resize import resize_linear_f32, resize_linear_u8
+from .cv_resize import resize_linear_f32, resize_linear_f32_ipp, resize_linear_u8
 
 # experiment.yaml:232-245 (controlled_variables.preprocessing) and transforms.py:37
 YOLO_SIZE = 640
@@ -238,7 +238,10 @@ def mobilenet_preprocess(crop: np.ndarray, size: int = MOBILENET_SIZE, resize=re
     """mobilenet_preprocess.py:114-160 -> float32[1,3,S,S] (uint8 or float32 crops)."""
     _check_image(crop, "crop", (np.uint8, np.float32))
     if crop.dtype == np.float32 and resize is resize_linear_u8:
-        resize = resize_linear_f32  # :204-206 float crops go through OpenCV's float path
+        # :204-206 float crops go through cv2's float path: Intel IPP in the opencv-python wheels the
+        # reference pins (IA_F32_RESIZE=opencv selects OpenCV's own generic path instead)
+        import os
+        resize = resize_linear_f32 if os.environ.get("IA_F32_RESIZE", "ipp").lower() == "opencv" else resize_linear_f32_ipp
     chw = imagenet_normalize(resize(crop, size, size)).transpose(2, 0, 1)
     return np.ascontiguousarray(chw[None])
 

@@ -57,3 +57,37 @@ def test_float32_resize_matches_cv2_generic_path(h, w):
         cv2.ipp.setUseIPP(was)
     assert np.array_equal(got, generic)
     assert np.allclose(got, with_ipp, rtol=0, atol=1e-4)
+
+
+F32_SHAPES = [(100, 100), (10, 10), (500, 800), (224, 224), (448, 448), (448, 224), (1, 1), (1, 300), (300, 1),
+              (2, 2), (3, 3), (300, 17), (17, 300), (223, 225), (449, 447), (672, 672), (896, 896), (64, 1000),
+              (31, 33), (57, 91), (225, 225), (2, 500), (112, 112), (1080, 1920)]
+
+
+@pytest.mark.parametrize("h,w", F32_SHAPES)
+def test_float32_resize_matches_cv2_with_ipp(h, w):
+    """The opencv-python wheels (what the reference pins and what this image has) hand float32
+    resizes to Intel IPP.  oracle.cv_resize.resize_linear_f32_ipp reproduces that result bit for bit,
+    on [0,1] and on [0,255] data."""
+    from oracle.cv_resize import resize_linear_f32_ipp
+
+    if not cv2.ipp.useIPP():
+        pytest.skip("this cv2 build has no IPP")
+    rng = np.random.default_rng(h * 4096 + w)
+    for top in (1.0, 255.0):
+        img = (rng.random((h, w, 3)) * top).astype(np.float32)
+        want = cv2.resize(img, (224, 224), interpolation=cv2.INTER_LINEAR)
+        assert np.array_equal(resize_linear_f32_ipp(img, 224, 224), want)
+
+
+def test_float32_resize_ipp_random_shapes():
+    from oracle.cv_resize import resize_linear_f32_ipp
+
+    if not cv2.ipp.useIPP():
+        pytest.skip("this cv2 build has no IPP")
+    rng = np.random.default_rng(77)
+    for _ in range(60):
+        h, w = (int(v) for v in rng.integers(1, 700, 2))
+        img = rng.random((h, w, 3)).astype(np.float32)
+        want = cv2.resize(img, (224, 224), interpolation=cv2.INTER_LINEAR)
+        assert np.array_equal(resize_linear_f32_ipp(img, 224, 224), want), (h, w)

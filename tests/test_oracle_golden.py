@@ -124,3 +124,28 @@ def test_validation_messages():
         P.mobilenet_preprocess(np.zeros((4, 4, 3), np.int32))
     with pytest.raises(ValueError, match="Invalid crop dimensions"):
         P.mobilenet_preprocess(np.zeros((0, 4, 3), np.uint8))
+
+
+def test_oracle_equals_the_staged_reference_modules():
+    """oracle/pipeline.py against the reference's OWN modules (baseline/_ref or /root/reference, via
+    oracle/refrun.py) on fresh inputs: the whole chain on uint8 frames, and MobileNetPreprocessor on
+    float32 crops — there the reference's cv2 uses Intel IPP and the oracle's IPP flavour must
+    give the same bits."""
+    from oracle import refrun
+    if refrun.find_reference() is None:
+        pytest.skip("reference files not staged")
+    cv2 = pytest.importorskip("cv2")
+    ref = refrun.Reference()
+    frames = synth.frames(2, 375, 500, seed=123)
+    heads = synth.head_v5(2, seed=124)
+    for f, h in zip(frames, heads):
+        a, b = ref.run_image(f, h, 0.25, 0.45), P.run_image(f, h, 0.25, 0.45)
+        for x, y in zip(a, b):
+            assert np.array_equal(np.asarray(x), np.asarray(y))
+    if not cv2.ipp.useIPP():
+        pytest.skip("this cv2 build has no IPP: float crops follow the generic path")
+    rng = np.random.default_rng(5)
+    for shape in ((100, 150), (448, 448), (37, 301), (500, 800), (1, 9)):
+        for top in (1.0, 255.0):
+            crop = (rng.random((*shape, 3)) * top).astype(np.float32)
+            assert np.array_equal(ref.mobilenet(crop).tensor, P.mobilenet_preprocess(crop)), (shape, top)
