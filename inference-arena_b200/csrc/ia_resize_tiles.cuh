@@ -693,8 +693,11 @@ static int launch_crops(const uint8_t* frames, size_t frames_bytes, int src_h, i
   c.out_w = c.out_h = c.canvas = out_size;
   c.canvas_x0 = c.canvas_y0 = 0;
   c.tiles_x = (out_size + kTeamConsumers - 1) / kTeamConsumers;
+  // a handful of ROIs (a single request) is latency-bound: shorter tiles spread it over more teams
   c.tile_rows = kTileRows;
-  c.tiles_y = (out_size + kTileRows - 1) / kTileRows;
+  while (c.tile_rows > 7 && (long long)roi_slots * c.tiles_x * ((out_size + c.tile_rows - 1) / c.tile_rows) < 2LL * kMaxTeams * 148)
+    c.tile_rows /= 2;
+  c.tiles_y = (out_size + c.tile_rows - 1) / c.tile_rows;
   c.fill_top = c.fill_bottom = c.fill_left = c.fill_right = 0;
   c.tiles_per_image = c.tiles_x * c.tiles_y;
   c.fill_rgb = 0;

@@ -17,7 +17,8 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 BENCH_NAME = {"letterbox_kernel": "K1_letterbox_normalize_chw", "decode_filter": "K2K3_decode_filter_nms",
-              "crop_resize_kernel": "K4_roi_crop_resize_normalize"}
+              "crop_resize_kernel": "K4_roi_crop_resize_normalize",
+              "resize_tiles_kernel": "K4_roi_crop_resize_normalize"}
 KEEP = ["Kernel Name", "Block Size", "Grid Size", "gpu__time_duration.sum", "dram__bytes_read.sum",
         "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
         "sm__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__issue_active.avg.pct_of_peak_sustained_active",
