@@ -137,7 +137,9 @@ int ia_decode_nms_static(const float* head_dev, int layout, int n, int anchors, 
 
 /* apply_nms() on already-decoded arrays, postprocess.py:76-160: boxes [m,4] cx,cy,w,h,
  * scores [m], class ids int32 [m] -> keep_dev int32 [max_det] (original indices),
- * count_dev [1], status_dev [1].  Workspace: ia_decode_nms_workspace_bytes(1, m, m). */
+ * count_dev [1], status_dev [1].  Workspace: ia_decode_nms_workspace_bytes(1, m, m).
+ * Class ids must lie in [0, 1023): the sort key holds a class in 10 bits (the Python wrapper
+ * renumbers arbitrary ids densely, as np.unique does in the reference, before it calls this). */
 int ia_nms(const float* boxes_dev, const float* scores_dev, const int32_t* class_ids_dev, int m,
            float conf_threshold, float iou_threshold, int max_det, int32_t* keep_dev,
            int32_t* count_dev, int32_t* status_dev, void* workspace_dev, size_t workspace_bytes,
@@ -173,7 +175,10 @@ int ia_scale_boxes_f64(const double* boxes_dev, int m, int cols, double scale, i
  *                   detection, is r = roi_offsets[i] + k
  *   roi_offsets_dev int32 [n+1] exclusive scan of min(count, max_det); [n] = total ROIs
  *   rois_dev        int32 [roi_capacity, 8] scratch/out: {image, x1, y1, x2, y2, empty,0,0}
- *                   (the integer crop rectangle extract_crop would use)
+ *                   (the integer crop rectangle extract_crop would use).  While the call runs,
+ *                   the two padding words of record 0 are its work counter (tiles are handed
+ *                   out one at a time so that crops of very different size finish together);
+ *                   they are 0 again when it completes.
  * ROIs beyond roi_capacity are not written (roi_offsets still reports the true total).
  * ------------------------------------------------------------------------------- */
 int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int src_h, int src_w,
