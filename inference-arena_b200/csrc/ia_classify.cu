@@ -16,9 +16,10 @@
 // a 64-bit key (ordered value bits : index).  Rows where that shortcut does not apply (NaN or
 // infinite logits, masses of equal values, k > 32) take k plain passes instead.
 //
-// Two kernels share that scheme: rows of up to 1024 classes (MobileNetV2: 1000) live in 32
-// registers per lane and never touch shared memory except for the candidate list; longer
-// rows are staged in shared memory.
+// Rows of up to 1024 classes (MobileNetV2: 1000) live in 32 registers per lane and never touch
+// shared memory except for the candidate list; their softmax sums a fast exponential and
+// chooses the candidates on the logits (see classify_topk_reg_kernel); longer rows are staged
+// in shared memory and follow the scheme above literally.
 #include <math_constants.h>
 
 #include "ia_common.cuh"
@@ -200,8 +201,11 @@ constexpr int kRegMaxClasses = kRegPerLane * 32;
 
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
 
+// Resident CTAs per SM.  The softmax variant is bound by how many rows are in flight, not by a
+// few spilled registers: 3 / 4 / 5 / 6 CTAs (80 / 64 / 48 / 40 registers) take 70 / 62 / 59 / 64 us
+// for 65 536 x 1000 logits.  The raw-value variant keeps a second 32-entry array and stays at 3.
 template <bool kSoftmax, bool kVec>
-__global__ void __launch_bounds__(kClassifyMaxWarps * 32, 3) classify_topk_reg_kernel(const ClassifyParams p) {
+__global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? 5 : 3) classify_topk_reg_kernel(const ClassifyParams p) {
   __shared__ float cand_raw[kClassifyMaxWarps][kCandidates];  // e (softmax) or the raw value
   __shared__ int cand_idx[kClassifyMaxWarps][kCandidates];
   __shared__ int cand_count[kClassifyMaxWarps];
@@ -230,73 +234,124 @@ __global__ void __launch_bounds__(kClassifyMaxWarps * 32, 3) classify_topk_reg_k
     for (int j = 0; j < kRegPerLane; ++j) x[j] = class_of(j) < C ? __ldg(g + class_of(j)) : -CUDART_INF_F;
   }
 
-  uint32_t u[kRegPerLane];  // ordered bits of what the selection compares (e or the raw value)
   float total = 0.f;
+  float m = 0.f;
   bool slow = k > 32;
+  bool has_nan = false;
+  int found = 0;
   if (kSoftmax) {
-    float m = x[0];
+    // Row maximum, then the sum of exp(s - max).  Only the k probabilities that are reported need
+    // numpy's exp to the last bits; the sum takes the fast exponential (FMUL + MUFU.EX2, relative
+    // error ~3e-7 on the terms that matter), which moves the reported values by as much — the
+    // tolerance of this row of SURVEY 8c is 1e-5.  Which classes win is decided on the logits:
+    // exp and the division are monotone, so every winner's logit is >= the k-th largest lane
+    // maximum; two different logits can round to one probability only if they are neighbours,
+    // so everything within 1e-5 below that bound is kept as a candidate, gets the accurate expf
+    // and the division, and the order among the candidates — ties included — is settled on those
+    // probabilities exactly as argsort(probs)[::-1] does.
+    m = x[0];
 #pragma unroll
     for (int j = 1; j < kRegPerLane; ++j) m = fmaxf(m, x[j]);  // a NaN is skipped here ...
+    const float lane_top = m;
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
+    // exp(x - m) = 2^(x * log2(e) - m * log2(e)): one FFMA + one MUFU.EX2 per element
+    constexpr float kLog2e = 1.4426950408889634f;
+    const float shift = __fmul_rn(-m, kLog2e);
+    float part[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int j = 0; j < kRegPerLane; ++j) x[j] = expf(__fsub_rn(x[j], m));  // ... and surfaces here
-    float part[kRegPerLane];
-#pragma unroll
-    for (int j = 0; j < kRegPerLane; ++j) part[j] = x[j];
-#pragma unroll
-    for (int w = kRegPerLane / 2; w > 0; w >>= 1)
-#pragma unroll
-      for (int j = 0; j < w; ++j) part[j] = __fadd_rn(part[j], part[j + w]);
-    double acc = (double)part[0];
+    for (int j = 0; j < kRegPerLane; ++j) {
+      float e;
+      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(__fmaf_rn(x[j], kLog2e, shift)));  // ... and surfaces here
+      part[j & 3] = __fadd_rn(part[j & 3], e);
+    }
+    double acc = (double)__fadd_rn(__fadd_rn(part[0], part[1]), __fadd_rn(part[2], part[3]));
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(kFull, acc, d);
     total = (float)acc;
-    // every e is in [0, 1] unless a logit was NaN or the row maximum infinite; then the sum
-    // is NaN and so is every probability (numpy gives the same) -> plain passes
+    // NaN logits, an infinite maximum or a row of -inf make the sum NaN, and then every
+    // probability is NaN (numpy gives the same) -> plain passes
     slow |= !(total == total);
+    float bound = 0.f;
+    if (!slow) {
+      bool alive = true;
+      const uint32_t top_bits = order_bits(lane_top);  // finite floats (padding is -inf): their order
+      uint32_t top = 0;
+      for (int j = 0; j < k; ++j) {
+        top = warp_max_u32(alive ? top_bits : 0u);
+        const uint32_t owners = __ballot_sync(kFull, alive && top_bits == top);
+        if (owners && lane == __ffs(owners) - 1) alive = false;
+      }
+      bound = __uint_as_float((top & 0x80000000u) ? (top & 0x7fffffffu) : ~top);
+      // where the k-th probability would be denormal the neighbour argument fails -> plain passes
+      slow = !(__fsub_rn(bound, m) >= -69.f);
+    }
+    if (!slow) {
+      if (lane == 0) cand_count[warp] = 0;
+      __syncwarp();
+      // which of this lane's elements lie within 1e-5 of the bound (2e-5 here: the subtraction
+      // rounds): one compare and one predicated bit per element, no branches
+      const float thr = __fsub_rn(bound, 2e-5f);
+      uint32_t hits = 0;
 #pragma unroll
-    for (int j = 0; j < kRegPerLane; ++j) u[j] = __float_as_uint(x[j]);  // e >= 0: bits are ordered
+      for (int j = 0; j < kRegPerLane; ++j)  // padding is -inf
+        asm("{ .reg .pred p; setp.ge.f32 p, %1, %2; @p or.b32 %0, %0, %3; }" : "+r"(hits) : "f"(x[j]), "f"(thr), "r"(1u << j));
+      // the few hits are read back through L1 (a register array cannot be indexed by a variable)
+      while (hits) {
+        const int j = __ffs(hits) - 1;
+        hits &= hits - 1;
+        const int cls = class_of(j);
+        const int pos = atomicAdd(&cand_count[warp], 1);
+        if (pos < kCandidates) cand_raw[warp][pos] = expf(__fsub_rn(__ldg(g + cls), m)), cand_idx[warp][pos] = cls;
+      }
+      __syncwarp();
+      found = cand_count[warp];
+      slow = found > kCandidates;
+    }
+    if (slow) {  // what the plain passes below work on: numpy's e, and their sum
+#pragma unroll
+      for (int j = 0; j < kRegPerLane; ++j) x[j] = expf(__fsub_rn(x[j], m));
+      float tree[kRegPerLane];
+#pragma unroll
+      for (int j = 0; j < kRegPerLane; ++j) tree[j] = x[j];
+#pragma unroll
+      for (int w = kRegPerLane / 2; w > 0; w >>= 1)
+#pragma unroll
+        for (int j = 0; j < w; ++j) tree[j] = __fadd_rn(tree[j], tree[j + w]);
+      double full = (double)tree[0];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) full += __shfl_xor_sync(kFull, full, d);
+      total = (float)full;
+    }
   } else {
+    uint32_t u[kRegPerLane];  // ordered bits of the raw values
 #pragma unroll
     for (int j = 0; j < kRegPerLane; ++j) u[j] = class_of(j) < C ? order_bits(x[j]) : 0u;
-  }
-  uint32_t lane_max = u[0];
+    uint32_t lane_max = u[0];
 #pragma unroll
-  for (int j = 1; j < kRegPerLane; ++j) lane_max = max(lane_max, u[j]);
-
-  bool has_nan = false;
-  if (!kSoftmax) has_nan = warp_max_u32(lane_max) == 0xffffffffu;  // NaN orders above everything
-
-  uint32_t bound = 0;
-  if (!slow) {
-    bool alive = true;
-    for (int j = 0; j < k; ++j) {
-      bound = warp_max_u32(alive ? lane_max : 0u);
-      const uint32_t owners = __ballot_sync(kFull, alive && lane_max == bound);
-      if (owners && lane == __ffs(owners) - 1) alive = false;
-    }
-    if (kSoftmax) {  // see classify_topk_kernel for the margin
-      const float e_bound = __uint_as_float(bound);
-      slow = !(e_bound >= 1e-30f);
-      bound = __float_as_uint(__fmul_rn(e_bound, 0.999999f));
-    }
-  }
-
-  int found = 0;
-  if (!slow) {
-    if (lane == 0) cand_count[warp] = 0;
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < kRegPerLane; ++j) {
-      if (u[j] >= bound) {  // padding holds 0 < bound
-        const int pos = atomicAdd(&cand_count[warp], 1);
-        if (pos < kCandidates) cand_raw[warp][pos] = x[j], cand_idx[warp][pos] = class_of(j);
+    for (int j = 1; j < kRegPerLane; ++j) lane_max = max(lane_max, u[j]);
+    has_nan = warp_max_u32(lane_max) == 0xffffffffu;  // NaN orders above everything
+    uint32_t bound = 0;
+    if (!slow) {
+      bool alive = true;
+      for (int j = 0; j < k; ++j) {
+        bound = warp_max_u32(alive ? lane_max : 0u);
+        const uint32_t owners = __ballot_sync(kFull, alive && lane_max == bound);
+        if (owners && lane == __ffs(owners) - 1) alive = false;
       }
+      if (lane == 0) cand_count[warp] = 0;
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < kRegPerLane; ++j) {
+        if (u[j] >= bound) {  // padding holds 0 < bound
+          const int pos = atomicAdd(&cand_count[warp], 1);
+          if (pos < kCandidates) cand_raw[warp][pos] = x[j], cand_idx[warp][pos] = class_of(j);
+        }
+      }
+      __syncwarp();
+      found = cand_count[warp];
+      slow = found > kCandidates;
     }
-    __syncwarp();
-    found = cand_count[warp];
-    slow = found > kCandidates;
   }
 
   const size_t out = (size_t)row * k;
