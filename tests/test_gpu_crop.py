@@ -179,3 +179,41 @@ def test_empty_rois_interleaved_with_real_ones(D):
     want = _oracle_crops(frames, dets, count, geom)
     assert int(rois[:, 5].sum()) >= n * kmax // 2
     assert np.array_equal(crops.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("out_size", [96, 225, 299, 512])
+def test_other_output_sizes(D, out_size):
+    """MobileNetPreprocessor(input_size=...) other than 224 (reference mobilenet_preprocess.py:58-112):
+    the tile kernel's generic-canvas instantiation, outputs wider than one 224-column tile, sizes
+    that are not multiples of 4, custom statistics; rectangles that up-scale, down-scale, copy
+    (= out_size) and halve exactly (2 x out_size)."""
+    h, w = 1100, 1300
+    frames = synth.frames(2, h, w, seed=900 + out_size)
+    rects = [[0, 10, 20, 10 + 37, 20 + 53, 0, 0, 0], [1, 0, 0, w, h, 0, 0, 0],
+             [0, 5, 7, 5 + out_size, 7 + out_size, 0, 0, 0], [1, 3, 1, 3 + 2 * out_size, 1 + 2 * out_size, 0, 0, 0],
+             [0, 100, 100, 100, 200, 1, 0, 0], [1, w - 3, h - 2, w, h, 0, 0, 0], [0, 0, 500, w, 501, 0, 0, 0]]
+    rois = np.array(rects, dtype=np.int32)
+    rois[:, 3] = np.minimum(rois[:, 3], w)
+    rois[:, 4] = np.minimum(rois[:, 4], h)
+    mean, std = (0.4, 0.5, 0.3), (0.25, 0.2, 0.3)
+    got = D.resize_normalize_rois_cuda(_dev(frames), _dev(rois), out_size, mean, std).cpu().numpy()
+    m32, s32 = np.array(mean, np.float32), np.array(std, np.float32)
+    for r, (img, x1, y1, x2, y2, empty, *_r) in enumerate(rois):
+        crop = np.zeros((1, 1, 3), np.uint8) if empty else np.ascontiguousarray(frames[img, y1:y2, x1:x2])
+        resized = O.resize_linear_u8(crop, out_size, out_size)
+        want = ((resized.astype(np.float32) / np.float32(255.0) - m32) / s32).transpose(2, 0, 1)
+        assert np.array_equal(got[r], want), (out_size, rois[r].tolist())
+
+
+@pytest.mark.parametrize("n", [1, 3, 70, 300])
+def test_k1_linear_mode_batch_sizes(D, n):
+    """K1's general linear mode runs in the tile kernel, whose tile height depends on the batch
+    size (small batches take shorter tiles): 1, 3, 70 and 300 frames of a COCO shape, every frame
+    of the small batches and a sample of the large ones against the oracle."""
+    h, w = 333, 500
+    frames = synth.frames(min(n, 8), h, w, seed=40 + n)
+    batch = np.ascontiguousarray(np.concatenate([frames] * ((n + len(frames) - 1) // len(frames)))[:n])
+    got = D.preprocess_batch_cuda(_dev(batch))
+    for i in sorted({0, n // 2, n - 1, *range(min(n, 4))}):
+        want, *_ = O.yolo_preprocess(batch[i])
+        assert np.array_equal(got[i : i + 1].cpu().numpy(), want), (n, i)
