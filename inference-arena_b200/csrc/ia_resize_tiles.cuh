@@ -73,7 +73,8 @@ struct TileParams {
   int teams;        // teams per CTA (blockDim.x = teams * kTeamThreads)
   int stage_bytes;  // bytes of ONE staging buffer (each team has kStages)
   // Work distribution.  With `tickets` (two zeroed ints: next tile, teams finished) a team draws
-  // its tiles one at a time; the last team to finish zeroes both again.  Without, teams stride.
+  // its tiles one at a time; the last team to finish zeroes both again.  Without, CTAs stride over
+  // the tiles and the teams of a CTA share a counter in shared memory.
   int* tickets;
   // ---- whole frames (rois == null): one resize geometry for the launch, so OpenCV's scales come
   // from the host and the x coefficients of every column are tabulated once per CTA
@@ -422,6 +423,7 @@ __device__ __forceinline__ AxisCoef x_entry(int mode, int x, double sc_x, int cw
 template <int kCanvas>
 __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kernel(const TileParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int cta_ticket;  // next of this CTA's tiles (used when there are no device-memory tickets)
   float* lut = reinterpret_cast<float*>(smem);  // [3][256][32]
   uint8_t* stage_all = smem + kLutFloats * sizeof(float);
   TeamCtl* ctl_all = reinterpret_cast<TeamCtl*>(stage_all + (size_t)p.teams * kStages * p.stage_bytes);
@@ -467,6 +469,7 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kern
       xtab[x] = make_int2(k.s0, k.w0 | (k.w1 << 16));
     }
   }
+  if (tid == 0) cta_ticket = 0;
   if (producer && lane == 0) {
 #pragma unroll
     for (int b = 0; b < kStages; ++b) {
@@ -486,7 +489,12 @@ __global__ void __launch_bounds__(kMaxTeams * kTeamThreads, 1) resize_tiles_kern
         it = lane == 0 ? atomicAdd(p.tickets, 1) : 0;
         it = __shfl_sync(0xffffffffu, it, 0);
       } else {
-        it = current < 0 ? (int)blockIdx.x * p.teams + team : current + n_teams;
+        // no counter in device memory: the CTA owns tiles blockIdx.x, blockIdx.x + gridDim.x, ... and
+        // its teams draw from those through a counter in shared memory (a team that gets cheap
+        // tiles simply takes more of them)
+        it = lane == 0 ? atomicAdd(&cta_ticket, 1) : 0;
+        it = __shfl_sync(0xffffffffu, it, 0);
+        it = (long long)it * gridDim.x + blockIdx.x < 0x7fffffffLL ? it * (int)gridDim.x + (int)blockIdx.x : -1;
       }
       return (it >= 0 && it < tiles) ? it : -1;
     };
@@ -648,6 +656,7 @@ static int launch_tiles(TileParams& c, int widest_cols, cudaStream_t stream) {
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   if (e != cudaSuccess) return (int)e;
+  optin -= 128;  // the kernel's few bytes of static shared memory count against the same limit
   // shared memory of the one CTA per SM: the table, then per team kStages staging buffers (each
   // at least two of the widest row segments) and a control block.  Narrow sources get four teams
   // of ~16 KB buffers; wide ones fewer teams with larger buffers.
