@@ -10,29 +10,32 @@
 // independent TEAMS of 7 consumer warps + 1 producer warp and one shared table of the output
 // values — ((v/255 - mean)/std) or v/divisor — replicated once per lane (bank) so that a warp's
 // 32 look-ups of 32 unrelated pixel values are one shared-memory wavefront.  A team takes tiles
-// one at a time (from a ticket counter in device memory when the caller has one: tiles of very
-// different cost still finish together) and walks a tile in steps of up to 14 rows, coupled
-// to its producer only by mbarriers (full / empty per staging buffer):
-//   producer: lane (row j, tap) evaluates OpenCV's yofs/beta entry, duplicates are removed
-//           with __match_any_sync and the copy geometry is worked out — all before waiting
-//           for the consumers to release the buffer; then the row plan and the step record are
-//           published and the needed segment of each distinct source row is pulled into the
-//           staging buffer with one 1-D bulk async copy (TMA engine, complete_tx on full[buf])
-//           of its 16-byte-aligned superset, clamped to the frame buffer (bytes a clamp cuts
-//           off are copied by the lane).  The next ticket and its ROI record are fetched
-//           while the current tile is staged.
+// one at a time — from a ticket counter in device memory when the caller has one, else from a
+// counter the teams of a CTA share over the CTA's own tiles: tiles of very different cost still
+// finish together — and walks a tile in steps, coupled to its producer only by mbarriers
+// (full / empty per staging buffer):
+//   producer: plans a whole tile at once, one lane per output row: OpenCV's yofs/beta entry,
+//           which of the consumers' two registers each source row goes to (its parity, so the
+//           taps of one output row never collide and every source row is staged and filled once
+//           per register), and the copy of each row (16-byte-aligned superset of the needed
+//           segment, clamped to the frame's allocation; bytes a clamp cuts off are copied by the
+//           lane).  A step is the longest run of rows whose fills fit a staging buffer (counted
+//           with ballots).  Per step: wait for the consumers to release the buffer, post the
+//           lanes' expect_tx, issue one 1-D bulk async copy per row (TMA engine, complete_tx on
+//           full[buf]), publish a 16-byte plan per output row and a 48-byte step record, arrive.
+//           The next ticket and its ROI record are fetched while the current tile is staged.
 //   consumers: a lane owns ONE output column for the whole tile and walks down the rows; a
 //           warp is 32 neighbouring columns, so every plane store is one 128-byte line.  The
-//           lane's x coefficients live in registers (no table in shared memory).  The
-//           horizontal pass of a source row — three aligned 32-bit shared loads + a funnel
-//           shift for the 6 bytes of the two taps, a PRMT pairing (p[c], p[c+3]) and one
-//           IDP.2A against the packed coefficient pair, >> 4 — is evaluated once per source
-//           row and kept in registers for as long as output rows use it (two rows are live:
-//           an up-scaled image reuses each ~2.5 times), which is the order cv::resize works in.
-//           The vertical step is two IMAD.HI against coefficients pre-shifted by 16 — OpenCV's
-//           11-bit fixed point, bit-identical to cv2.resize INTER_LINEAR (copy and the exact-2x
-//           box average use the same arithmetic with tables a0=b0=2048 resp.
-//           a0=a1=b0=b1=1024, which reduce to the identity and to (p00+p01+p10+p11+2)>>2).
+//           lane's x coefficients live in registers.  The horizontal pass of a source row —
+//           three aligned 32-bit shared loads + a funnel shift for the 6 bytes of the two taps,
+//           a PRMT pairing (p[c], p[c+3]) and one IDP.2A against the packed coefficient pair,
+//           >> 4 — is evaluated once per source row and kept in registers for as long as output
+//           rows use it (two rows are live: an up-scaled image reuses each ~2.5 times), which is
+//           the order cv::resize works in.  The vertical step is two IMAD.HI against
+//           coefficients pre-shifted by 16 — OpenCV's 11-bit fixed point, bit-identical to
+//           cv2.resize INTER_LINEAR (copy and the exact-2x box average use the same arithmetic
+//           with tables a0=b0=2048 resp. a0=a1=b0=b1=1024, which reduce to the identity and to
+//           (p00+p01+p10+p11+2)>>2).  Consumers never read global memory.
 // The global side sees only wide, fully used requests; byte gathers hit shared memory.
 #pragma once
 
