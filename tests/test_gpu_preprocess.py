@@ -97,3 +97,38 @@ def test_full_size_batch_properties(D):
 def test_empty_batch(D):
     out = D.preprocess_batch_cuda(torch.empty((0, 480, 640, 3), dtype=torch.uint8, device="cuda"))
     assert out.shape == (0, 3, 640, 640)
+
+
+def test_two_host_threads_with_different_shapes(D):
+    """include/ia_b200.h promises that calls on different streams may run concurrently from
+    different host threads.  Two threads preprocess frames of different shapes (different resize
+    modes, different shared-memory sizes: the per-kernel shared-memory cap is raised once, never
+    re-set per launch) and crop different ROI sets, each on its own stream, many times over."""
+    import threading
+
+    cases = [(synth.frames(3, 480, 640, seed=1), None), (synth.frames(3, 1080, 1920, seed=2), None),
+             (synth.frames(2, 375, 500, seed=3), None), (synth.frames(2, 2160, 3840, seed=4), None)]
+    cases = [(f, np.concatenate([O.yolo_preprocess(x)[0] for x in f])) for f, _ in cases]
+    errors = []
+
+    def worker(k):
+        try:
+            stream = torch.cuda.Stream()
+            with torch.cuda.stream(stream):
+                for it in range(40):
+                    frames, want = cases[(k + it) % len(cases)] if it % 2 else cases[k]
+                    got = D.preprocess_batch_cuda(_dev(frames))
+                    rois = torch.tensor([[0, 0, 0, frames.shape[2], frames.shape[1], 0, 0, 0]], dtype=torch.int32).cuda()
+                    crop = D.resize_normalize_rois_cuda(_dev(frames), rois)
+                    stream.synchronize()
+                    if not np.array_equal(got.cpu().numpy(), want):
+                        errors.append(("K1", k, it))
+                    if it == 0 and not np.array_equal(crop.cpu().numpy(), O.mobilenet_preprocess(frames[0])):
+                        errors.append(("K4", k, it))
+        except Exception as e:  # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors[:5]
