@@ -379,12 +379,13 @@ def stage_benchmarks(dev, steps: int, warmup: int, peak_gbs: float) -> dict:
         torch.cuda.synchronize(dev)
         ok = int(batch.status.sum().item()) == 0
         ms = time_loop(batch.rerun, max(steps // 4, 10), 3, dev)
-        t0 = time.perf_counter()
-        reps = 5
-        for _ in range(reps):
+        calls = []  # host wall clock per call (parse, upload, six launches): the median of seven
+        for _ in range(7):
+            t0 = time.perf_counter()
             last = J.decode_jpeg_batch_cuda(blobs, dev)
-        torch.cuda.synchronize(dev)
-        call_ms = (time.perf_counter() - t0) / reps * 1e3
+            torch.cuda.synchronize(dev)
+            calls.append((time.perf_counter() - t0) * 1e3)
+        call_ms = sorted(calls)[len(calls) // 2]
         t0 = time.perf_counter()
         for b in files:
             cv2.cvtColor(cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR), cv2.COLOR_BGR2RGB)

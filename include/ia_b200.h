@@ -180,6 +180,10 @@ int ia_scale_boxes_f64(const double* boxes_dev, int m, int cols, double scale, i
  *                   out one at a time so that crops of very different size finish together);
  *                   they are 0 again when it completes.
  * ROIs beyond roi_capacity are not written (roi_offsets still reports the true total).
+ * Two staged rows of the widest possible crop must fit the SM's shared memory next to the
+ * look-up table: frames wider than about 10 800 pixels (10 816 on B200) return
+ * IA_ERR_UNSUPPORTED before anything is launched; the same bound applies to max_src_w of the
+ * ragged form and to src_w of ia_resize_normalize_rois.
  * ------------------------------------------------------------------------------- */
 int ia_crop_resize_normalize(const uint8_t* frames_dev, int n, int src_h, int src_w,
                              const float* dets_dev, const int32_t* count_dev, int max_det,

@@ -201,11 +201,56 @@ constexpr int kRegMaxClasses = kRegPerLane * 32;
 
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
 
+// Two float32 lanes per instruction (sm_100 f32x2): (d0, d1) = (a0, a1) * b + c and (s0, s1) += (e0, e1),
+// each lane rounded to nearest exactly like the scalar instruction.
+__device__ __forceinline__ void fma_f32x2(float& d0, float& d1, float a0, float a1, float b, float c) {
+  uint64_t a, bb, cc, d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(bb) : "f"(b));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(cc) : "f"(c));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(bb), "l"(cc));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
+__device__ __forceinline__ void add_f32x2(float& s0, float& s1, float e0, float e1) {
+  uint64_t a, b, d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(s0), "f"(s1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(e0), "f"(e1));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(s0), "=f"(s1) : "l"(d));
+}
+
+// A lower bound of the k-th largest of the 32 lanes' ordered keys (k <= 32), within 32 steps of
+// it.  The low five bits of every key are replaced by the lane number: the keys become distinct,
+// so a round is one warp maximum and "was it mine" — no vote for who owns a tie; clearing those
+// bits is monotone, so the k-th largest of the cleared keys is the cleared k-th largest.
+__device__ __forceinline__ uint32_t kth_largest_lane_key(uint32_t key, int lane, int k) {
+  uint32_t mine = (key & ~31u) | (uint32_t)lane, top = 0;
+#pragma unroll 1  // k is a run-time value: the unrolled forms cost more in loop control than a round
+  for (int j = 0; j < k; ++j) {
+    top = warp_max_u32(mine);
+    mine = mine == top ? 0u : mine;  // (a key of 0 is lane 0's at most: still distinct)
+  }
+  return top & ~31u;
+}
+
+// Order-preserving bits of a float that is not NaN (-0 sorts just below +0, which no bound minds),
+// and back.
+__device__ __forceinline__ uint32_t order_bits_no_nan(float x) {
+  const uint32_t b = __float_as_uint(x);
+  return b ^ ((uint32_t)((int32_t)b >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ float from_order_bits(uint32_t u) {
+  return __uint_as_float(u ^ ((u & 0x80000000u) ? 0x80000000u : 0xffffffffu));
+}
+
 // Resident CTAs per SM.  The softmax variant is bound by how many rows are in flight, not by a
 // few spilled registers: 3 / 4 / 5 / 6 CTAs (80 / 64 / 48 / 40 registers) take 70 / 62 / 59 / 64 us
 // for 65 536 x 1000 logits.  The raw-value variant keeps a second 32-entry array and stays at 3.
+#ifndef IA_N4_CTAS
+#define IA_N4_CTAS 5
+#endif
 template <bool kSoftmax, bool kVec>
-__global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? 5 : 3) classify_topk_reg_kernel(const ClassifyParams p) {
+__global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? IA_N4_CTAS : 3) classify_topk_reg_kernel(const ClassifyParams p) {
   __shared__ float cand_raw[kClassifyMaxWarps][kCandidates];  // e (softmax) or the raw value
   __shared__ int cand_idx[kClassifyMaxWarps][kCandidates];
   __shared__ int cand_count[kClassifyMaxWarps];
@@ -222,12 +267,20 @@ __global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? 5 : 3) clas
   auto class_of = [lane](int j) { return kVec ? ((j >> 2) * 32 + lane) * 4 + (j & 3) : j * 32 + lane; };
   float x[kRegPerLane];
   if (kVec) {
-#pragma unroll
-    for (int q = 0; q < kRegPerLane / 4; ++q) {
+    // group q of a lane is in range for every lane once classes >= (q + 1) * 128: rows of 897+
+    // classes (MobileNetV2's 1000) need the check — and the -inf filler — for the last group only
+    auto load_group = [&](int q, bool checked) {
       const int i = (q * 32 + lane) * 4;
-      const float4 f = i < C ? __ldg(reinterpret_cast<const float4*>(g + i))
-                             : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+      const float4 f = !checked || i < C ? __ldg(reinterpret_cast<const float4*>(g + i))
+                                         : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
       x[4 * q] = f.x, x[4 * q + 1] = f.y, x[4 * q + 2] = f.z, x[4 * q + 3] = f.w;
+    };
+    if (C > (kRegPerLane / 4 - 1) * 128) {  // uniform: two straight-line copies of the loads
+#pragma unroll
+      for (int q = 0; q < kRegPerLane / 4; ++q) load_group(q, q == kRegPerLane / 4 - 1);
+    } else {
+#pragma unroll
+      for (int q = 0; q < kRegPerLane / 4; ++q) load_group(q, true);
     }
   } else {
 #pragma unroll
@@ -258,31 +311,27 @@ __global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? 5 : 3) clas
     // exp(x - m) = 2^(x * log2(e) - m * log2(e)): one FFMA + one MUFU.EX2 per element
     constexpr float kLog2e = 1.4426950408889634f;
     const float shift = __fmul_rn(-m, kLog2e);
+    // (the packed f32x2 forms, FFMA2 / FADD2: the same roundings, half the issue slots)
     float part[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int j = 0; j < kRegPerLane; ++j) {
-      float e;
-      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(__fmaf_rn(x[j], kLog2e, shift)));  // ... and surfaces here
-      part[j & 3] = __fadd_rn(part[j & 3], e);
+    for (int j = 0; j < kRegPerLane; j += 2) {
+      float t0, t1, e0, e1;
+      fma_f32x2(t0, t1, x[j], x[j + 1], kLog2e, shift);
+      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(t0));  // ... and surfaces here
+      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(t1));
+      add_f32x2(part[j & 2], part[(j & 2) + 1], e0, e1);
     }
-    double acc = (double)__fadd_rn(__fadd_rn(part[0], part[1]), __fadd_rn(part[2], part[3]));
+    // (an xor butterfly adds the same pairs in every lane: all lanes hold the same bits)
+    total = __fadd_rn(__fadd_rn(part[0], part[1]), __fadd_rn(part[2], part[3]));
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(kFull, acc, d);
-    total = (float)acc;
+    for (int d = 16; d > 0; d >>= 1) total = __fadd_rn(total, __shfl_xor_sync(kFull, total, d));
     // NaN logits, an infinite maximum or a row of -inf make the sum NaN, and then every
     // probability is NaN (numpy gives the same) -> plain passes
     slow |= !(total == total);
     float bound = 0.f;
     if (!slow) {
-      bool alive = true;
-      const uint32_t top_bits = order_bits(lane_top);  // finite floats (padding is -inf): their order
-      uint32_t top = 0;
-      for (int j = 0; j < k; ++j) {
-        top = warp_max_u32(alive ? top_bits : 0u);
-        const uint32_t owners = __ballot_sync(kFull, alive && top_bits == top);
-        if (owners && lane == __ffs(owners) - 1) alive = false;
-      }
-      bound = __uint_as_float((top & 0x80000000u) ? (top & 0x7fffffffu) : ~top);
+      // (the sum is not NaN, so no logit is: every lane maximum is a number or the padding's -inf)
+      bound = from_order_bits(kth_largest_lane_key(order_bits_no_nan(lane_top), lane, k));
       // where the k-th probability would be denormal the neighbour argument fails -> plain passes
       slow = !(__fsub_rn(bound, m) >= -69.f);
     }
@@ -333,12 +382,7 @@ __global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? 5 : 3) clas
     has_nan = warp_max_u32(lane_max) == 0xffffffffu;  // NaN orders above everything
     uint32_t bound = 0;
     if (!slow) {
-      bool alive = true;
-      for (int j = 0; j < k; ++j) {
-        bound = warp_max_u32(alive ? lane_max : 0u);
-        const uint32_t owners = __ballot_sync(kFull, alive && lane_max == bound);
-        if (owners && lane == __ffs(owners) - 1) alive = false;
-      }
+      bound = kth_largest_lane_key(lane_max, lane, k);
       if (lane == 0) cand_count[warp] = 0;
       __syncwarp();
 #pragma unroll
@@ -355,7 +399,33 @@ __global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? 5 : 3) clas
   }
 
   const size_t out = (size_t)row * k;
-  if (!slow) {
+  if (!slow && found <= 32) {
+    // The usual case, k..2k candidates: one per lane.  A round finds the largest ordered value
+    // (and, among equal values, the id the tie rule prefers); the lane that holds it takes rank j
+    // and retires; every ranked lane stores its own result at the end.  (found >= k: the maximum
+    // is never the 0 of a retired or empty lane.)
+    float v = 0.f;
+    uint32_t vb = 0, id = 0;
+    if (lane < found) {
+      v = kSoftmax ? __fdiv_rn(cand_raw[warp][lane], total) : cand_raw[warp][lane];
+      // a probability is finite and >= 0: its raw bits are ordered already
+      vb = kSoftmax ? (__float_as_uint(v) | 0x80000000u) : order_bits(v);
+      id = (uint32_t)cand_idx[warp][lane] ^ flip;
+    }
+    int rank = -1;
+#pragma unroll 1
+    for (int j = 0; j < k; ++j) {
+      // two maxima, no branch: the value, then — among the lanes that hold it, nearly always
+      // one — the tie rule's id (candidates are distinct classes: exactly one lane matches both)
+      const uint32_t top = warp_max_u32(vb);
+      const uint32_t best = warp_max_u32(vb == top ? id : 0u);
+      if (vb == top && id == best) rank = j, vb = 0;
+    }
+    if (rank >= 0) {
+      p.ids[out + rank] = (int)(id ^ flip);
+      p.values[out + rank] = v;
+    }
+  } else if (!slow) {
     // lane L owns candidates L and L+32: value to report, then its 64-bit key
     float v0 = 0.f, v1 = 0.f;
     uint64_t c0 = 0ull, c1 = 0ull;

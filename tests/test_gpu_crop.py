@@ -217,3 +217,20 @@ def test_k1_linear_mode_batch_sizes(D, n):
     for i in sorted({0, n // 2, n - 1, *range(min(n, 4))}):
         want, *_ = O.yolo_preprocess(batch[i])
         assert np.array_equal(got[i : i + 1].cpu().numpy(), want), (n, i)
+
+
+def test_widest_frames(D):
+    """include/ia_b200.h: two staged rows of the widest crop must fit shared memory.  A 10 000-pixel-wide
+    frame (one team per SM, the largest staging buffers) is still bit-exact; 12 000 is refused with
+    IA_ERR_UNSUPPORTED before any launch, and the context stays usable."""
+    frames = synth.frames(1, 6, 10000, seed=77)
+    rois = np.array([[0, 0, 0, 10000, 6, 0, 0, 0], [0, 17, 1, 9999, 5, 0, 0, 0], [0, 9000, 0, 9001, 6, 0, 0, 0]], np.int32)
+    got = D.resize_normalize_rois_cuda(torch.from_numpy(frames).cuda(), torch.from_numpy(rois).cuda(), 224).cpu().numpy()
+    for r, (_, x1, y1, x2, y2, *_r) in enumerate(rois):
+        want = O.mobilenet_preprocess(np.ascontiguousarray(frames[0, y1:y2, x1:x2]))
+        assert np.array_equal(got[r:r + 1], want), r
+    wide = torch.zeros((1, 2, 12000, 3), dtype=torch.uint8, device="cuda")
+    with pytest.raises(RuntimeError, match="unsupported"):
+        D.resize_normalize_rois_cuda(wide, torch.tensor([[0, 0, 0, 12000, 2, 0, 0, 0]], dtype=torch.int32, device="cuda"), 224)
+    again = D.resize_normalize_rois_cuda(torch.from_numpy(frames).cuda(), torch.from_numpy(rois[:1]).cuda(), 224).cpu().numpy()
+    assert np.array_equal(again, got[:1])
