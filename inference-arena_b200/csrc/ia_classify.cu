@@ -243,14 +243,17 @@ __device__ __forceinline__ float from_order_bits(uint32_t u) {
   return __uint_as_float(u ^ ((u & 0x80000000u) ? 0x80000000u : 0xffffffffu));
 }
 
-// Resident CTAs per SM.  The softmax variant is bound by how many rows are in flight, not by a
-// few spilled registers: 3 / 4 / 5 / 6 CTAs (80 / 64 / 48 / 40 registers) take 70 / 62 / 59 / 64 us
-// for 65 536 x 1000 logits.  The raw-value variant keeps a second 32-entry array and stays at 3.
-#ifndef IA_N4_CTAS
-#define IA_N4_CTAS 5
-#endif
+// Resident CTAs per SM.  The softmax variant is bound by instruction issue with the warps it has
+// resident (~70 % of the issue slots: chains of warp reductions and shuffles), not by a few
+// spilled registers: 4 / 5 / 6 CTAs (64 / 48 / 40 registers) take 56 / 51 / 54 us for 65 536 x
+// 1000 logits.  The raw-value variant keeps a second 32-entry array and stays at 3.  Measured
+// and dropped: a persistent form, every warp walking many rows with the next row's bulk copy in
+// flight in a staging buffer (the issue slots stay ~70 % busy either way, and its 80 extra
+// instructions per row made it 12 % slower); listing candidates by class and taking their
+// expf once, converged, after the loop (19 fewer instructions per row, 2 % slower).
+constexpr int kSoftmaxCtasPerSm = 5;
 template <bool kSoftmax, bool kVec>
-__global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? IA_N4_CTAS : 3) classify_topk_reg_kernel(const ClassifyParams p) {
+__global__ void __launch_bounds__(kClassifyMaxWarps * 32, kSoftmax ? kSoftmaxCtasPerSm : 3) classify_topk_reg_kernel(const ClassifyParams p) {
   __shared__ float cand_raw[kClassifyMaxWarps][kCandidates];  // e (softmax) or the raw value
   __shared__ int cand_idx[kClassifyMaxWarps][kCandidates];
   __shared__ int cand_count[kClassifyMaxWarps];

@@ -52,6 +52,42 @@ def test_softmax_topk_vs_oracle(D, rows, classes, k):
     assert not status.any()
 
 
+@pytest.mark.parametrize("rows,classes,k", [(12000, 1000, 5), (6500, 1024, 5), (7000, 896, 3), (9000, 128, 5),
+                                            (8000, 4, 2), (6001, 900, 32)])
+def test_many_rows(D, rows, classes, k):
+    """More rows than the GPU holds warps at once (5 920 on a B200), several waves of CTAs.  Every row
+    against numpy; rows with NaN, infinities, nothing but -inf, ties and constants are mixed in —
+    those leave the fast path inside the same launch."""
+    logits = synth.logits(rows, seed=700 + classes, classes=classes)
+    special = {}
+    if classes >= 128:
+        logits[17, 3] = np.nan
+        logits[rows - 1, 7] = np.inf
+        logits[4000, :] = -np.inf
+        logits[4001, 5] = logits[4001, 77] = 60.0
+        logits[5999, :] = 1.5
+        special = {17, rows - 1, 4000, 4001, 5999}
+    ids, vals, status = _run(D, logits, k)
+    with np.errstate(invalid="ignore"):
+        e = np.exp(logits - logits.max(axis=1, keepdims=True))
+        probs = e / e.sum(axis=1, keepdims=True)
+    want_ids = np.argsort(probs, axis=1, kind="stable")[:, ::-1][:, :k]
+    top = min(k, 5, classes)  # the generator separates the first five
+    plain = np.array([r not in special for r in range(rows)])
+    assert np.array_equal(ids[plain][:, :top], want_ids[plain][:, :top])
+    want_vals = np.take_along_axis(probs, want_ids, axis=1)
+    np.testing.assert_allclose(vals[plain], want_vals[plain], rtol=RTOL, atol=1e-30)
+    assert all(len(set(row.tolist())) == k for row in ids[::97])
+    for r in special:
+        o_ids, o_probs = O.softmax_topk(logits[r], k)
+        if np.isnan(o_probs).all():
+            assert np.isnan(vals[r]).all() and ids[r].tolist() == o_ids.tolist(), r
+        else:
+            np.testing.assert_allclose(vals[r], o_probs, rtol=RTOL, atol=1e-30)
+            assert ids[r, :2].tolist() == o_ids[:2].tolist(), r
+    assert set(np.nonzero(status)[0].tolist()) == ({17} if special else set())
+
+
 def test_unaligned_rows_take_the_scalar_loads(D):
     logits = synth.logits(9, seed=640)
     flat = torch.empty(logits.size + 1, dtype=torch.float32, device="cuda")
