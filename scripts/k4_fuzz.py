@@ -1,7 +1,8 @@
 """Ad-hoc differential fuzz of the tile kernel: random frame shapes (odd pitches, 1-pixel sides, wide
 frames that get fewer teams), random rectangles and output sizes through ia_resize_normalize_rois and
 the detection-driven ia_crop_resize_normalize, plus K1's linear mode on random shapes / targets /
-batch sizes, all compared bit for bit with the oracle.  argv[1] = number of rounds (default 40)."""
+batch sizes, all compared bit for bit with the oracle.  argv[1] = number of rounds (default 40),
+argv[2] = seed (default 2026)."""
 import sys
 from pathlib import Path
 R = Path(__file__).resolve().parent.parent
@@ -13,7 +14,7 @@ from shared.processing import device as D
 from workloads import synth
 
 rounds = int(sys.argv[1]) if len(sys.argv) > 1 else 40
-rng = np.random.default_rng(2026)
+rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 2026)
 dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
 bad = 0
 for it in range(rounds):
