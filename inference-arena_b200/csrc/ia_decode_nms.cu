@@ -395,7 +395,12 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsParams p) {
       int kc = 0;
       int seg_cls = s_seg_cls, seg_start = s_seg_start;
       const int j0 = lane, j1 = lane + 32;
-      while (alive && kc < kLazyRows) {
+      // Every class run of the block keeps at least its first live box: with more runs than lazy
+      // rows the loop below cannot finish the block and would only delay the parallel path.
+      const unsigned run0 = __ballot_sync(0xffffffffu, j0 < nb && (j0 == 0 || bcls[j0] != bcls[j0 - 1]));
+      const unsigned run1 = __ballot_sync(0xffffffffu, j1 < nb && bcls[j1] != bcls[j1 - 1]);
+      const int lazy_rows = __popc(run0) + __popc(run1) > kLazyRows ? 0 : kLazyRows;
+      while (alive && kc < lazy_rows) {
         const int i = __ffsll((long long)alive) - 1;
         const int ci = bcls[i];
         if (lane == 0) klist[kc] = i;
@@ -439,24 +444,44 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsParams p) {
         if (lane == 0) rowmask[i] = (uint64_t)lo | ((uint64_t)hi << 32);
       }
       __syncthreads();
-      if (tid == 0) {
+      if (warp == 0) {
+        // Greedy resolve.  Only a row that suppresses something can change the outcome, so the
+        // serial walk (every lane, the same words) visits those rows alone, in order, each only
+        // if its box is still alive when its turn comes; what is alive at the end is kept.
+        const int j0 = lane, j1 = lane + 32;
+        const bool nz0 = ((pending >> j0) & 1ull) && rowmask[j0] != 0;
+        const bool nz1 = ((pending >> j1) & 1ull) && rowmask[j1] != 0;
+        uint64_t todo = (uint64_t)__ballot_sync(0xffffffffu, nz0) | ((uint64_t)__ballot_sync(0xffffffffu, nz1) << 32);
         uint64_t alive = pending;
-        int kc = s_kcount;
-        int seg_cls = s_seg_cls, seg_start = s_seg_start;
-        while (alive) {
-          const int i = __ffsll((long long)alive) - 1;
-          klist[kc] = i;
-          if (bcls[i] != seg_cls) {
-            seg_cls = bcls[i];
-            seg_start = K + kc;
-          }
-          ++kc;
-          alive &= ~rowmask[i];
-          alive &= ~(1ull << i);
+        while (todo) {
+          const int i = __ffsll((long long)todo) - 1;
+          todo &= todo - 1;
+          if ((alive >> i) & 1ull) alive &= ~rowmask[i];
         }
-        s_kcount = kc;
-        s_seg_cls = seg_cls;
-        s_seg_start = seg_start;
+        // the kept boxes in order: position = boxes kept before it
+        const int kc0 = s_kcount;
+        const bool k0 = (alive >> j0) & 1ull, k1 = (alive >> j1) & 1ull;
+        if (k0) klist[kc0 + __popcll(alive & ((1ull << j0) - 1ull))] = j0;
+        if (k1) klist[kc0 + __popcll(alive & ((1ull << j1) - 1ull))] = j1;
+        // the class run the next block may continue: the last kept box's, from its first kept box
+        // (classes ascend: if that class is the one already open, the run simply goes on)
+        int seg_cls = s_seg_cls, seg_start = s_seg_start;
+        if (alive) {
+          const int cl = bcls[63 - __clzll((long long)alive)];
+          if (cl != seg_cls) {
+            const uint64_t same = (uint64_t)__ballot_sync(0xffffffffu, k0 && bcls[j0] == cl) |
+                                  ((uint64_t)__ballot_sync(0xffffffffu, k1 && bcls[j1] == cl) << 32);
+            const int f = __ffsll((long long)same) - 1;
+            seg_cls = cl;
+            seg_start = K + kc0 + __popcll(alive & ((1ull << f) - 1ull));
+          }
+        }
+        __syncwarp();
+        if (lane == 0) {
+          s_kcount = kc0 + __popcll(alive);
+          s_seg_cls = seg_cls;
+          s_seg_start = seg_start;
+        }
       }
       __syncthreads();
     }

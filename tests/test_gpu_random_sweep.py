@@ -90,6 +90,26 @@ def test_k2k3_random_heads(D):
             assert np.array_equal(dets[i, :k].cpu().numpy(), want_dets)
 
 
+def test_k2k3_random_heads_many_classes(D):
+    """As above with 9..80 classes in play: blocks of 64 sorted candidates then hold more class runs
+    than the lazy rows of K3's resolve, which goes straight to the row-parallel path, and most
+    rows suppress nothing (the serial walk visits only those that do)."""
+    rng = np.random.default_rng(777)
+    for case in range(10):
+        anchors = int(rng.integers(64, 4000))
+        cand = int(rng.integers(1, min(anchors, 700) + 1))
+        conf, iou = float(rng.choice([0.25, 0.5])), float(rng.choice([0.45, 0.2, 0.7]))
+        head = synth.head_v5_dense(2, seed=3500 + case, candidates=cand, anchors=anchors, classes=80,
+                                   used_classes=int(rng.integers(9, 81)))
+        synth.assert_tie_free(head, conf)
+        dets, keep, count, status = D.decode_nms_cuda(_dev(head), conf, iou, max_det=anchors)
+        for i in range(2):
+            want_dets, want_keep = O.detect_v5(head[i], conf, iou)
+            k = int(count[i])
+            assert int(status[i]) == 0 and keep[i, :k].cpu().tolist() == want_keep, (anchors, cand, case)
+            assert np.array_equal(dets[i, :k].cpu().numpy(), want_dets)
+
+
 def test_jpeg_random_files():
     """Random sizes, sampling modes, qualities, restart intervals, table optimisation, content
     (photo-like, noise, flat), orientation tags — one mixed batch per round, against cv2.imdecode
