@@ -6,6 +6,7 @@ run in the K4 kernel with the crop as a single whole-image ROI.
 
 from __future__ import annotations
 
+import functools
 from dataclasses import dataclass
 
 import numpy as np
@@ -27,9 +28,13 @@ class MobileNetPreprocessResult:
     original_shape: tuple[int, int]
 
 
-def _whole_image_rois(shapes: list[tuple[int, int]]) -> torch.Tensor:
-    rows = [[i, 0, 0, w, h, 0, 0, 0] for i, (h, w) in enumerate(shapes)]
-    return torch.tensor(rows, dtype=torch.int32)
+@functools.lru_cache(maxsize=1024)
+def _whole_image_roi_on(device_index: int, height: int, width: int) -> torch.Tensor:
+    """The one-rectangle table {image 0, x1 0, y1 0, x2 w, y2 h, not empty} of a (height, width)
+    crop, kept on the device: the kernel only reads it, and a service sees the same few hundred
+    crop shapes again and again."""
+    row = torch.tensor([[0, 0, 0, width, height, 0, 0, 0]], dtype=torch.int32)
+    return row.to(torch.device("cuda", device_index))
 
 
 class MobileNetPreprocessor:
@@ -53,7 +58,7 @@ class MobileNetPreprocessor:
                                                     IMAGENET_STD)
             return MobileNetPreprocessResult(tensor=_hostio.to_host(tensor), original_shape=(height, width))
         frames = _hostio.to_device(crop)[None]
-        rois = _whole_image_rois([(height, width)]).to(frames.device)
+        rois = _whole_image_roi_on(frames.device.index, height, width)
         # like the reference (mobilenet_preprocess.py:146 -> transforms.py:270) the module-level
         # ImageNet statistics are applied, not self.mean / self.std
         tensor = _dev.resize_normalize_rois_cuda(frames, rois, self.input_size, IMAGENET_MEAN, IMAGENET_STD)

@@ -249,3 +249,26 @@ def test_load_image_from_bytes_uses_the_device_decoder_and_keeps_cv2_pixels(sp, 
         load_image_from_bytes(b"not an image at all")
     with pytest.raises(ValueError, match="Failed to decode"):
         load_image_from_bytes(golden["jpeg0_bytes"].tobytes()[:200])  # a JPEG cut inside its headers
+
+
+def test_results_come_back_in_recycled_pinned_blocks(monkeypatch):
+    """_hostio.to_host: large results are page-locked arrays whose blocks go back to torch's caching
+    host allocator when the caller drops them; beyond the cap they are ordinary arrays; values are
+    the same either way."""
+    import gc
+    from shared.processing import YOLOPreprocessor, _hostio
+    img = synth.frames(1, 480, 640, seed=5)[0]
+    want, *_ = O.yolo_preprocess(img)
+    gc.collect()
+    before = _hostio.pinned_result_bytes()
+    res = YOLOPreprocessor()(img)
+    assert np.array_equal(res.tensor, want) and res.tensor.flags.writeable
+    assert _hostio.pinned_result_bytes() - before == res.tensor.nbytes
+    kept = res.tensor[:, :, :8].copy()
+    del res
+    gc.collect()
+    assert _hostio.pinned_result_bytes() == before
+    assert np.array_equal(kept, want[:, :, :8])
+    monkeypatch.setattr(_hostio, "_PINNED_CAP", 0)
+    res = YOLOPreprocessor()(img)
+    assert np.array_equal(res.tensor, want) and _hostio.pinned_result_bytes() == before
