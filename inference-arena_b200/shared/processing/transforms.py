@@ -4,8 +4,9 @@
     letterbox            transforms.py:118-180   -> ia_letterbox_u8
     scale_boxes          transforms.py:183-230   -> ia_scale_boxes
     imagenet_normalize   transforms.py:238-272   -> ia_imagenet_normalize_u8
-    load_image(_from_bytes) transforms.py:45-110 -> image decode stays on the host
-                         (libjpeg via cv2; outside the accelerated path)
+    load_image(_from_bytes) transforms.py:45-110 -> baseline JPEGs: shared.processing.jpeg
+                         (device decoder); everything else, and damaged files:
+                         cv2 on the host, as in the reference
 """
 
 from __future__ import annotations
@@ -21,8 +22,36 @@ IMAGENET_STD: np.ndarray = np.array(_mobilenet_config["std"], dtype=np.float32)
 LETTERBOX_COLOR: tuple[int, int, int] = (114, 114, 114)
 
 
+def _decode_jpeg_on_device(data: bytes) -> tuple[np.ndarray | None, bool]:
+    """(RGB pixels, False) for a baseline JPEG decoded on the GPU.  (None, False): the host decoder
+    has to take the file — not a JPEG the device decoder handles, or a damaged one (libjpeg's
+    concealment is cv2's to apply).  (None, True): the data ends before the last block, which is
+    where ``cv2.imdecode`` gives up and returns None."""
+    if data[:2] != b"\xff\xd8":
+        return None, False
+    from shared.processing import jpeg as _jpeg
+    try:
+        batch = _jpeg.decode_jpeg_batch_cuda([data])
+    except _jpeg.UnsupportedJpeg:
+        return None, False
+    status = int(batch.status[0])  # synchronises
+    if status == 0:
+        return _hostio.to_host(batch.frames[0]), False
+    return None, bool(status & 2)
+
+
 def load_image(image_path: str) -> np.ndarray:
-    """Decode an image file to RGB uint8 [H, W, 3] (host side)."""
+    """Decode an image file to RGB uint8 [H, W, 3] (reference transforms.py:45-74): an intact
+    baseline JPEG on the GPU like ``load_image_from_bytes``, everything else — and every path
+    that cannot be read — through ``cv2.imread`` as in the reference."""
+    try:
+        with open(image_path, "rb") as fh:
+            data = fh.read()
+    except (OSError, TypeError, ValueError):
+        data = b""
+    pixels, _ = _decode_jpeg_on_device(data)
+    if pixels is not None:
+        return pixels
     import cv2
 
     bgr = cv2.imread(image_path, cv2.IMREAD_COLOR)
@@ -43,17 +72,11 @@ def load_image_from_bytes(image_bytes: bytes) -> np.ndarray:
     if not image_bytes:
         raise ValueError("Failed to decode image from bytes: empty input")
     data = bytes(image_bytes)
-    if data[:2] == b"\xff\xd8":
-        from shared.processing import jpeg as _jpeg
-        try:
-            batch = _jpeg.decode_jpeg_batch_cuda([data])
-            status = int(batch.status[0])  # synchronises
-            if status == 0:
-                return batch.frames[0].cpu().numpy()
-            if status & 2:  # the data ends before the last block: cv2.imdecode returns None here
-                raise ValueError("Failed to decode image from bytes")
-        except _jpeg.UnsupportedJpeg:
-            pass
+    pixels, truncated = _decode_jpeg_on_device(data)
+    if pixels is not None:
+        return pixels
+    if truncated:
+        raise ValueError("Failed to decode image from bytes")
     import cv2
 
     bgr = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)

@@ -251,6 +251,40 @@ def test_load_image_from_bytes_uses_the_device_decoder_and_keeps_cv2_pixels(sp, 
         load_image_from_bytes(golden["jpeg0_bytes"].tobytes()[:200])  # a JPEG cut inside its headers
 
 
+def test_load_image_reads_files_like_cv2_imread(sp, golden, tmp_path):
+    """load_image (reference transforms.py:45-74): JPEG files through the device decoder, other
+    formats, damaged files and unreadable paths exactly as cv2.imread leaves them."""
+    cv2 = pytest.importorskip("cv2")
+    from shared.processing.transforms import load_image
+
+    def imread_rgb(path):
+        return cv2.cvtColor(cv2.imread(str(path), cv2.IMREAD_COLOR), cv2.COLOR_BGR2RGB)
+
+    for i in (0, 3, 7):
+        path = tmp_path / f"g{i}.jpg"
+        path.write_bytes(golden[f"jpeg{i}_bytes"].tobytes())
+        got = load_image(str(path))
+        assert np.array_equal(got, golden[f"jpeg{i}_rgb"]) and np.array_equal(got, imread_rgb(path))
+    img = synth.frames(1, 40, 56, seed=9)[0]
+    png = tmp_path / "x.png"
+    cv2.imwrite(str(png), cv2.cvtColor(img, cv2.COLOR_RGB2BGR))
+    assert np.array_equal(load_image(str(png)), img)
+    damaged = tmp_path / "damaged.jpg"
+    damaged.write_bytes((__import__("pathlib").Path(__file__).parent / "golden" / "jpeg_idct_overflow_case.jpg").read_bytes())
+    assert np.array_equal(load_image(str(damaged)), imread_rgb(damaged))
+    cut = tmp_path / "cut.jpg"
+    data = golden["jpeg0_bytes"].tobytes()
+    cut.write_bytes(data[: len(data) // 2])  # cv2 conceals or refuses: whatever it does is the answer
+    want = cv2.imread(str(cut), cv2.IMREAD_COLOR)
+    if want is None:
+        with pytest.raises(ValueError, match="Failed to load image"):
+            load_image(str(cut))
+    else:
+        assert np.array_equal(load_image(str(cut)), cv2.cvtColor(want, cv2.COLOR_BGR2RGB))
+    with pytest.raises(ValueError, match="Failed to load image: /no/such/file.jpg"):
+        load_image("/no/such/file.jpg")
+
+
 def test_results_come_back_in_recycled_pinned_blocks(monkeypatch):
     """_hostio.to_host: large results are page-locked arrays whose blocks go back to torch's caching
     host allocator when the caller drops them; beyond the cap they are ordinary arrays; values are
