@@ -1,5 +1,5 @@
 """Ad-hoc (torchrun): the host-buffer leg of bench.py alone, for several (chunk, slots) settings of
-HostPipeline, max over ranks.  torchrun --nproc-per-node N scripts/e2e_sweep.py"""
+HostPipeline, max over ranks.  torchrun --nproc-per-node N scripts/e2e_sweep.py [CHUNKxSLOTS ...]"""
 import os
 import sys
 from pathlib import Path
@@ -17,8 +17,9 @@ if world > 1:
 B, steps = 256, 4
 frames = torch.randint(0, 256, (B, 1080, 1920, 3), dtype=torch.uint8).pin_memory()
 from workloads import synth
-heads = torch.from_numpy(synth.head_v5(B, seed=5 + rank)).pin_memory()  # ~4 detections per image, as in bench.py
-for chunk, slots in ((32, 3), (64, 2), (16, 4), (64, 3), (128, 2)):
+heads = torch.from_numpy(synth.head_v5(16, seed=5 + rank)).repeat(B // 16, 1, 1).pin_memory()  # ~4 detections per image, as in bench.py
+settings = [tuple(int(v) for v in a.split("x")) for a in sys.argv[1:]] or [(32, 3), (64, 2), (16, 4), (64, 3), (128, 2)]
+for chunk, slots in settings:
     hp = HostPipeline(B, 1080, 1920, dev, chunk=chunk, slots=slots, max_det=32, max_candidates=4096, rois_per_image=8)
     hp.run(frames, heads)
     if world > 1:
