@@ -215,6 +215,7 @@ __device__ __forceinline__ void letterbox_body(const PreParams& p, const uint8_t
     const RowPlan rp = plan[j];
     const uint8_t* p0 = smem + rp.off0;
     const uint8_t* p1 = smem + rp.off1;
+    (void)p1;  // (only the modes with a second tap row read it)
     uint32_t px[4][3];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
